@@ -1,0 +1,143 @@
+/*
+ * radnerf_b200.h -- C ABI of libradnerf_b200.so (hand-written CUDA for sm_100a).
+ *
+ * This is the drop-in boundary for Rad-NeRF's sampling -> K sub-NeRFs -> gated compositing
+ * hot path.  Every entry point names the reference interface it replaces (paths relative
+ * to the thu-nics/Rad-NeRF tree).  Conventions:
+ *   - plain pointers + sizes; every data pointer is a DEVICE pointer unless the parameter
+ *     name ends in `_host`; buffers are dense row-major with the shapes written beside them;
+ *   - nothing is allocated inside the library except through an explicit rnb_*_create();
+ *     callers hand in every output buffer (outputs need NOT be zero-filled: kernels write
+ *     every element they own, which removes the reference's 256 MiB memsets);
+ *   - `stream` is a cudaStream_t (0 = legacy default stream, what the reference uses);
+ *   - return value: 0 on success, a negative RNB_ERR_* otherwise; rnb_last_error() gives a
+ *     thread-local message.  Launch errors are detected with cudaPeekAtLastError().
+ */
+#ifndef RADNERF_B200_H_
+#define RADNERF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* rnb_stream_t;
+
+#define RNB_OK 0
+#define RNB_ERR_BADARG (-1)   /* null pointer / negative size / unsupported configuration */
+#define RNB_ERR_LAUNCH (-2)   /* CUDA launch or runtime failure */
+#define RNB_ERR_NOMEM (-3)
+
+#define RNB_ABI_VERSION 1
+
+int rnb_abi_version(void);
+const char* rnb_last_error(void);
+/* compute capability of the current device as major*10+minor (100 on B200); <0 on error */
+int rnb_device_arch(void);
+
+/* ------------------------------------------------------------------------------------
+ * (1) intersection / morton / packbits  -- replaces vren.ray_aabb_intersect,
+ *     vren.ray_sphere_intersect, vren.morton3D, vren.morton3D_invert, vren.packbits
+ * ------------------------------------------------------------------------------------ */
+
+/* models/csrc/binding.cpp:4-16 -> intersection.cu:5-100.
+ * rays_o, rays_d (n_rays,3) f32; centers, half_sizes (n_voxels,3) f32.
+ * out: hit_cnt (n_rays) i32; hits_t (n_rays,max_hits,2) f32, -1 = no hit;
+ *      hits_voxel_idx (n_rays,max_hits) i64, -1 = no hit.  Rows are ordered by ascending
+ *      hits_t[...,0] exactly as the reference's torch::sort does (unfilled -1 rows first). */
+int rnb_ray_aabb_intersect(const float* rays_o, const float* rays_d, const float* centers,
+                           const float* half_sizes, int64_t n_rays, int64_t n_voxels, int max_hits,
+                           int32_t* hit_cnt, float* hits_t, int64_t* hits_voxel_idx,
+                           rnb_stream_t stream);
+
+/* binding.cpp:19-31 -> intersection.cu:103-197.  radii (n_spheres) f32. */
+int rnb_ray_sphere_intersect(const float* rays_o, const float* rays_d, const float* centers,
+                             const float* radii, int64_t n_rays, int64_t n_spheres, int max_hits,
+                             int32_t* hit_cnt, float* hits_t, int64_t* hits_sphere_idx,
+                             rnb_stream_t stream);
+
+/* binding.cpp:46-50 -> raymarching.cu:62-88.  coords (n,3) i32 -> indices (n) i32. */
+int rnb_morton3D(const int32_t* coords, int64_t n, int32_t* indices, rnb_stream_t stream);
+/* binding.cpp:53-57 -> raymarching.cu:90-119.  indices (n) i32 -> coords (n,3) i32. */
+int rnb_morton3D_invert(const int32_t* indices, int64_t n, int32_t* coords, rnb_stream_t stream);
+
+/* binding.cpp:34-43 -> raymarching.cu:122-161.  density_grid (8*n_bytes) f32 (or f16 when
+ * grid_is_half != 0); bitfield (n_bytes) u8, bit i of byte n = grid[8n+i] > threshold. */
+int rnb_packbits(const void* density_grid, int grid_is_half, int64_t n_bytes, float threshold,
+                 uint8_t* density_bitfield, rnb_stream_t stream);
+/* Same, with the threshold read from device memory: thr = min(*mean_density, threshold_cap)
+ * (networks.py:405-406 without the .item() host sync). */
+int rnb_packbits_devthr(const float* density_grid, int64_t n_bytes, const float* mean_density,
+                        float threshold_cap, uint8_t* density_bitfield, rnb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * (2) occupancy-grid ray marching -- replaces vren.raymarching_train / raymarching_test
+ * ------------------------------------------------------------------------------------ */
+
+/* binding.cpp:60-81 -> raymarching.cu:166-332, split in two phases so that the caller owns
+ * the data-dependent allocation.  Phase 1 marches every ray once, and writes
+ *   rays_a (n_rays,3) i64 = [ray_idx, start_idx, N_samples] in ASCENDING RAY ORDER with
+ *   start_idx = exclusive prefix sum of N_samples (a deterministic, legal outcome of the
+ *   reference's atomicAdd slot reservation, raymarching.cu:237-241), and
+ *   counter (2) i32 = [total_samples, n_rays]   (the reference's `counter`).
+ * hits_t is (n_rays,2) f32 (t1 = -1 for a miss); noise (n_rays) f32 in [0,1). */
+int rnb_raymarching_train_count(const float* rays_o, const float* rays_d, const float* hits_t,
+                                const uint8_t* density_bitfield, int cascades, float scale,
+                                float exp_step_factor, const float* noise, int grid_size,
+                                int max_samples, int64_t n_rays,
+                                int64_t* rays_a, int32_t* counter, rnb_stream_t stream);
+/* Phase 2: re-march and write xyzs, dirs (cap,3) f32 and deltas, ts (cap) f32 for the
+ * samples whose slot is < cap (cap >= counter[0] gives the reference result). */
+int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, const float* hits_t,
+                                const uint8_t* density_bitfield, int cascades, float scale,
+                                float exp_step_factor, const float* noise, int grid_size,
+                                int max_samples, int64_t n_rays, const int64_t* rays_a, int64_t cap,
+                                float* xyzs, float* dirs, float* deltas, float* ts,
+                                rnb_stream_t stream);
+
+/* binding.cpp:84-106 -> raymarching.cu:335-454.  hits_t (n_rays_total,2) f32 is MUTATED
+ * ([r][0] <- resume point).  alive_indices (n_alive) i64.  Outputs (n_alive,N_samples[,3])
+ * f32 are fully written (unused slots = 0, like the reference's zero-filled slabs) and
+ * N_eff_samples (n_alive) i32.  Reproduces hazard Q1 (calc_dt is handed `cascades` where the
+ * train kernel hands `scale`, raymarching.cu:370,399). */
+int rnb_raymarching_test(const float* rays_o, const float* rays_d, float* hits_t,
+                         const int64_t* alive_indices, int64_t n_alive,
+                         const uint8_t* density_bitfield, int cascades, float scale,
+                         float exp_step_factor, int grid_size, int max_samples, int N_samples,
+                         float* xyzs, float* dirs, float* deltas, float* ts,
+                         int32_t* N_eff_samples, rnb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * (5) volume compositing -- replaces vren.composite_train_fw / _bw / composite_test_fw
+ * ------------------------------------------------------------------------------------ */
+
+/* binding.cpp:109-126 -> volumerendering.cu:6-84.  sigmas, deltas, ts (N) f32; rgbs (N,3)
+ * f32; rays_a (n_rays,3) i64.  out: total_samples (n_rays) i64 indexed by ray_idx; opacity,
+ * depth (n_rays), rgb (n_rays,3) indexed by ray_idx; ws (N) (0 after early termination). */
+int rnb_composite_train_fw(const float* sigmas, const float* rgbs, const float* deltas,
+                           const float* ts, const int64_t* rays_a, float T_threshold,
+                           int64_t n_rays, int64_t N, int64_t* total_samples, float* opacity,
+                           float* depth, float* rgb, float* ws, rnb_stream_t stream);
+
+/* binding.cpp:129-163 -> volumerendering.cu:87-203.  out: dL_dsigmas (N), dL_drgbs (N,3). */
+int rnb_composite_train_bw(const float* dL_dopacity, const float* dL_ddepth, const float* dL_drgb,
+                           const float* dL_dws, const float* sigmas, const float* rgbs,
+                           const float* ws, const float* deltas, const float* ts,
+                           const int64_t* rays_a, const float* opacity, const float* depth,
+                           const float* rgb, float T_threshold, int64_t n_rays, int64_t N,
+                           float* dL_dsigmas, float* dL_drgbs, rnb_stream_t stream);
+
+/* binding.cpp:166-194 -> volumerendering.cu:206-286.  sigmas, deltas, ts (n_alive,N_samples);
+ * rgbs (n_alive,N_samples,3); alive_indices (n_alive) i64 MUTATED (-1 = finished);
+ * opacity, depth (n_rays_total), rgb (n_rays_total,3) accumulated IN PLACE. */
+int rnb_composite_test_fw(const float* sigmas, const float* rgbs, const float* deltas,
+                          const float* ts, const float* hits_t, int64_t* alive_indices,
+                          float T_threshold, const int32_t* N_eff_samples, int64_t n_alive,
+                          int N_samples, float* opacity, float* depth, float* rgb,
+                          rnb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RADNERF_B200_H_ */

@@ -1,0 +1,92 @@
+"""ctypes binding of libradnerf_b200.so (C ABI declared in include/radnerf_b200.h).
+
+The library is plain CUDA (no torch types cross the boundary): this module hands it raw
+device pointers (`tensor.data_ptr()`), sizes and the current CUDA stream.  There is NO CPU
+fallback: if the shared library is missing, every operator raises ``RuntimeError``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libradnerf_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "radnerf_b200.h")
+
+_lib = None
+
+
+class RadNerfB200Error(RuntimeError):
+    pass
+
+
+def declared_symbols() -> list[str]:
+    """Every `rnb_*` function declared in include/radnerf_b200.h."""
+    with open(HEADER_PATH) as f:
+        src = f.read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(rnb_[A-Za-z0-9_]+)\s*\(", src)))
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RadNerfB200Error(
+                f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(make -C rad-nerf_b200/csrc). There is no CPU fallback.")
+        _lib = ctypes.CDLL(LIB_PATH)
+        _lib.rnb_last_error.restype = ctypes.c_char_p
+        for name in declared_symbols():
+            fn = getattr(_lib, name)  # raises AttributeError if the header and the .so disagree
+            if name not in ("rnb_last_error",):
+                fn.restype = ctypes.c_int
+    return _lib
+
+
+def _arg(a):
+    """tensor -> device pointer; None -> NULL; python scalars pass through typed."""
+    if a is None:
+        return ctypes.c_void_p(0)
+    if isinstance(a, torch.Tensor):
+        return ctypes.c_void_p(a.data_ptr())
+    return a
+
+
+def i64(v):
+    return ctypes.c_int64(int(v))
+
+
+def i32(v):
+    return ctypes.c_int(int(v))
+
+
+def f32(v):
+    return ctypes.c_float(float(v))
+
+
+def stream_arg(device=None):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def call(name: str, *args):
+    """Call `rnb_<name>`; raises RadNerfB200Error with the library's message on failure."""
+    fn = getattr(lib(), name)
+    rc = fn(*[_arg(a) for a in args])
+    if rc != 0:
+        msg = lib().rnb_last_error()
+        raise RadNerfB200Error(f"{name} failed ({rc}): {msg.decode() if msg else ''}")
+
+
+def check_input(x: torch.Tensor, name: str, dtype=None):
+    """Same contract as the reference's CHECK_INPUT (models/csrc/include/utils.h:4-6):
+    CUDA + contiguous, else RuntimeError; plus a dtype check the reference lacks."""
+    if not x.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if not x.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if dtype is not None and x.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {x.dtype}")
