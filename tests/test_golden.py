@@ -1,0 +1,109 @@
+"""Pins the oracle (CPU, always) and the product kernels (GPU) to golden vectors produced by
+the reference's OWN kernels (tests/golden/make_golden_vren.py ran the unmodified
+/root/reference/models/csrc sources, compiled for sm_100a, on a B200).
+Integer outputs bit-exact; fp32 marching outputs bit-exact; compositing within the
+__expf-vs-expf tolerance on CPU and ~1 ulp reassociation on GPU."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import CONFIGS, GOLDEN, get_scene
+from oracle import vren_cpu as O
+from radnerf_b200 import synthetic as syn
+
+
+def load(name):
+    p = os.path.join(GOLDEN, f"vren_{name}.npz")
+    if not os.path.exists(p):
+        pytest.skip("golden fixture missing")
+    return np.load(p)
+
+
+def canon_rays_a(counts):
+    n = len(counts)
+    return np.stack([np.arange(n), np.concatenate([[0], np.cumsum(counts)[:-1]]), counts], 1).astype(np.int64)
+
+
+@pytest.mark.parametrize("cfg", list(CONFIGS))
+def test_oracle_matches_reference_golden(cfg):
+    g = load(cfg)
+    scale, esf, C = float(g["scale"]), float(g["esf"]), int(g["cascades"])
+    sc, bf = get_scene(scale)
+    assert np.float32(sc.threshold) == g["threshold"]
+    # packbits digest
+    pb = O.packbits(sc.density_grid, sc.threshold)
+    assert np.unpackbits(pb).sum() == g["packbits_popcount"]
+    assert np.array_equal(pb[:4096], g["packbits_head"])
+    assert np.bitwise_xor.reduce(pb.view(np.uint32)) == g["packbits_xor32"]
+    # morton
+    assert np.array_equal(O.morton3D(g["morton_coords"]), g["morton_idx"])
+    assert np.array_equal(O.morton3D_invert(g["morton_idx"]), g["morton_inv"])
+    # aabb
+    cnt, ht, hi = O.ray_aabb_intersect(g["rays_o"], g["rays_d"], np.zeros(3), np.full(3, scale))
+    assert np.array_equal(cnt, g["aabb_cnt"]) and np.array_equal(hi, g["aabb_idx"])
+    assert np.array_equal(ht.view(np.uint32), g["aabb_t"].view(np.uint32))
+    # training march: counts, and bit-exact payload
+    ra, x, d, dl, ts, c = O.raymarching_train(g["rays_o"], g["rays_d"], g["hits_t"], bf, C, scale, esf, g["noise"])
+    assert c[0] == g["train_total"] and np.array_equal(ra[:, 2].astype(np.int32), g["train_counts"])
+    for a, b in ((x, g["train_xyzs"]), (dl, g["train_deltas"]), (ts, g["train_ts"])):
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    # composite fw/bw (expf vs __expf tolerance)
+    T, op, dp, col, ws = O.composite_train_fw(g["sigmas"], g["rgbs"], dl, ts, ra, 1e-4)
+    assert np.abs(ws - g["fw_ws"]).max() < 2e-6 and np.abs(op - g["fw_opacity"]).max() < 1e-5
+    assert np.abs(col - g["fw_rgb"]).max() < 1e-5 and np.abs(dp - g["fw_depth"]).max() < 1e-5 * max(1, ts.max())
+    assert (T != g["fw_total"]).mean() < 0.02
+    gs, gc = O.composite_train_bw(g["gO"], g["gD"], g["gC"], g["gW"], g["sigmas"], g["rgbs"], g["fw_ws"], dl, ts, ra,
+                                  g["fw_opacity"], g["fw_depth"], g["fw_rgb"], 1e-4)
+    assert np.abs(gc - g["bw_drgbs"]).max() < 1e-5
+    assert np.abs(gs - g["bw_dsigmas"]).max() < 1e-4 * max(1.0, np.abs(g["bw_dsigmas"]).max())
+    # test-time marching, 3 resumed rounds + in-place compositing
+    hits = g["hits_t"].copy()
+    n = len(hits)
+    op = np.zeros(n, np.float32); dp = np.zeros(n, np.float32); col = np.zeros((n, 3), np.float32)
+    for rnd in range(3):
+        alive = g[f"test{rnd}_alive_in"].copy()
+        x, d, dl, ts, ne = O.raymarching_test(g["rays_o"], g["rays_d"], hits, alive, bf, C, scale, esf, 128, 1024, 4)
+        assert np.array_equal(ne, g[f"test{rnd}_neff"])
+        assert np.array_equal(x.view(np.uint32), g[f"test{rnd}_xyzs"].view(np.uint32))
+        assert np.array_equal(ts.view(np.uint32), g[f"test{rnd}_ts"].view(np.uint32))
+        assert np.array_equal(dl.view(np.uint32), g[f"test{rnd}_deltas"].view(np.uint32))
+        assert np.array_equal(hits.view(np.uint32), g[f"test{rnd}_hits_t"].view(np.uint32))
+        O.composite_test_fw(g[f"test{rnd}_sigmas"], g[f"test{rnd}_rgbs"], dl, ts, hits, alive, 1e-4, ne, op, dp, col)
+        assert (alive != g[f"test{rnd}_alive_out"]).mean() < 0.01
+        assert np.abs(op - g[f"test{rnd}_opacity"]).max() < 1e-5 and np.abs(col - g[f"test{rnd}_rgb"]).max() < 1e-5
+        # continue from the reference's state so rounds stay comparable
+        op, dp, col = g[f"test{rnd}_opacity"].copy(), g[f"test{rnd}_depth"].copy(), g[f"test{rnd}_rgb"].copy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", list(CONFIGS))
+def test_product_matches_reference_golden(cfg):
+    import torch
+    from radnerf_b200 import vren
+    g = load(cfg)
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    scale, esf, C = float(g["scale"]), float(g["esf"]), int(g["cascades"])
+    sc, bf = get_scene(scale)
+    pb = torch.zeros(len(bf), dtype=torch.uint8, device="cuda")
+    vren.packbits(cu(sc.density_grid), sc.threshold, pb)
+    pbn = pb.cpu().numpy()
+    assert np.unpackbits(pbn).sum() == g["packbits_popcount"] and np.array_equal(pbn[:4096], g["packbits_head"])
+    assert np.bitwise_xor.reduce(pbn.view(np.uint32)) == g["packbits_xor32"]
+    assert np.array_equal(vren.morton3D(cu(g["morton_coords"])).cpu().numpy(), g["morton_idx"])
+    cnt, ht, hi = vren.ray_aabb_intersect(cu(g["rays_o"]), cu(g["rays_d"]), torch.zeros(1, 3, device="cuda"),
+                                          torch.full((1, 3), scale, device="cuda"), 1)
+    assert np.array_equal(ht.cpu().numpy().view(np.uint32), g["aabb_t"].view(np.uint32))
+    ra, x, d, dl, ts, c = vren.raymarching_train(cu(g["rays_o"]), cu(g["rays_d"]), cu(g["hits_t"]), pb, C, scale, esf,
+                                                 cu(g["noise"]), 128, 1024)
+    assert int(c[0]) == g["train_total"] and np.array_equal(ra[:, 2].cpu().numpy().astype(np.int32), g["train_counts"])
+    assert np.array_equal(x.cpu().numpy().view(np.uint32), g["train_xyzs"].view(np.uint32))
+    assert np.array_equal(ts.cpu().numpy().view(np.uint32), g["train_ts"].view(np.uint32))
+    T, op, dp, col, ws = vren.composite_train_fw(cu(g["sigmas"]), cu(g["rgbs"]), dl, ts, ra, 1e-4)
+    assert np.array_equal(T.cpu().numpy(), g["fw_total"])
+    assert np.array_equal(ws.cpu().numpy().view(np.uint32), g["fw_ws"].view(np.uint32))
+    assert np.abs(col.cpu().numpy() - g["fw_rgb"]).max() < 2e-6
+    gs, gc = vren.composite_train_bw(cu(g["gO"]), cu(g["gD"]), cu(g["gC"]), cu(g["gW"]), cu(g["sigmas"]), cu(g["rgbs"]), ws,
+                                     dl, ts, ra, op, dp, col, 1e-4)
+    assert np.abs(gc.cpu().numpy() - g["bw_drgbs"]).max() < 1e-6
+    assert np.abs(gs.cpu().numpy() - g["bw_dsigmas"]).max() < 1e-4 * max(1.0, np.abs(g["bw_dsigmas"]).max())

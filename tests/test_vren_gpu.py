@@ -193,11 +193,14 @@ def test_raymarching_train_edge_cases():
                                                             torch.rand(256, device="cuda"), 128, 1024)
     assert counter.tolist() == [0, 256] and xyzs.shape[0] == 0
     assert rays_a[:, 0].tolist() == list(range(256)) and int(rays_a[:, 1:].abs().sum()) == 0
-    # fully occupied grid: max_samples cap is honoured
-    full = torch.full((128 ** 3 // 8,), 255, dtype=torch.uint8, device="cuda")
-    o, d, h = make_rays(0.5, 512)
-    rays_a, *_ = vren.raymarching_train(cu(o), cu(d), cu(h), full, 1, 0.5, 0.0, torch.zeros(512, device="cuda"), 128, 64)
-    assert int(rays_a[:, 2].max()) == 64
+    # fully occupied unbounded grid: the max_samples cap is honoured and matches the oracle
+    full = np.full(6 * 128 ** 3 // 8, 255, np.uint8)
+    o, d, h = make_rays(16.0, 512)
+    rays_a, *_ = vren.raymarching_train(cu(o), cu(d), cu(h), cu(full), 6, 16.0, 1 / 256, torch.zeros(512, device="cuda"), 128, 8)
+    assert int(rays_a[:, 2].max()) == 8
+    from oracle import vren_cpu as O
+    ora, _ = O.raymarching_train(o, d, h, full, 6, 16.0, 1 / 256, np.zeros(512, np.float32), 128, 8, count_only=True)
+    assert np.array_equal(rays_a.cpu().numpy(), ora)
 
 
 # ---- marching (test time) ---------------------------------------------------------------------
