@@ -137,6 +137,59 @@ int rnb_composite_test_fw(const float* sigmas, const float* rgbs, const float* d
                           int N_samples, float* opacity, float* depth, float* rgb,
                           rnb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * (3) multiresolution hash-grid encoding + SH4 -- replaces tinycudann's
+ *     Encoding{Grid/Hash} and Encoding{SphericalHarmonics,4}
+ *     (reference call sites: models/networks.py:42-55, 70-77, 234-256; tinycudann itself is
+ *      not vendored in the reference -- published algorithm, see oracle/tcnn_cpu.py)
+ * ------------------------------------------------------------------------------------ */
+
+#define RNB_MAX_LEVELS 32
+typedef struct {
+  int32_t n_levels;                    /* L (16)                                           */
+  int32_t n_features;                  /* F (2; only 2 is implemented)                     */
+  float scale[RNB_MAX_LEVELS];         /* s_l = N_min * b^l - 1                            */
+  uint32_t res[RNB_MAX_LEVELS];        /* ceil(s_l) + 1                                    */
+  uint32_t offset[RNB_MAX_LEVELS + 1]; /* first ENTRY of level l in the flat table         */
+} rnb_grid_meta;
+
+/* x (n,3) f32 in [0,1]; table (n_entries,2) f16 (level-major, entry, feature -- tcnn's
+ * `params` layout rounded to fp16); out (n, 2L) f16. */
+int rnb_hashgrid_fwd(const float* x, int64_t n, const void* table_f16, const rnb_grid_meta* meta,
+                     void* out_f16, rnb_stream_t stream);
+/* Scatter-add of dL/dout (n,2L) f16 into grad_table (n_entries,2) f32 (ACCUMULATES: the
+ * table is shared by all K sub-NeRFs, the caller zeroes it once per step).  grad_scale
+ * multiplies every contribution (1/loss_scale). */
+int rnb_hashgrid_bwd(const float* x, int64_t n, const void* dL_dout_f16, const rnb_grid_meta* meta,
+                     float grad_scale, float* grad_table, rnb_stream_t stream);
+/* u (n,3) f32 in [0,1] (the reference feeds (d/|d|+1)/2, networks.py:322-323) -> (n,16) f16 */
+int rnb_sh4_fwd(const float* u, int64_t n, void* out_f16, rnb_stream_t stream);
+/* fp32 master parameters -> fp16 compute copy (n elements) */
+int rnb_cast_f32_to_f16(const float* src, int64_t n, void* dst_f16, rnb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * (4) 64-wide fp16 MLPs on tensor cores -- replaces tinycudann Network{FullyFusedMLP}
+ *     (reference call sites: models/networks.py:269-289, 1075-1085)
+ * ------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t in_width;        /* padded to a multiple of 16 (pad columns hold 1.0, as tcnn) */
+  int32_t out_width;       /* padded to a multiple of 16                                 */
+  int32_t n_hidden;        /* hidden layers of 64 neurons (ReLU)                         */
+  int32_t out_activation;  /* 0 = None, 1 = Sigmoid                                      */
+} rnb_mlp_desc;
+
+/* weights: fp16 copy of tcnn's flat `params`: row-major (out,in) matrices
+ * [64 x in_width | (n_hidden-1) x 64 x 64 | out_width x 64].  in (n,in_width) f16 ->
+ * out (n,out_width) f16.  hidden (n_hidden, n, 64) f16 receives the post-ReLU activations
+ * needed by the backward pass (may be NULL for inference). */
+int rnb_mlp_fwd(const rnb_mlp_desc* desc, const void* weights_f16, const void* in_f16, int64_t n,
+                void* out_f16, void* hidden_f16, rnb_stream_t stream);
+/* dL_din (n,in_width) f16 may be NULL (no input gradient wanted); grad_weights (same layout
+ * as weights, f32) is ACCUMULATED into, scaled by grad_scale; may be NULL. */
+int rnb_mlp_bwd(const rnb_mlp_desc* desc, const void* weights_f16, const void* in_f16,
+                const void* hidden_f16, const void* out_f16, const void* dL_dout_f16, int64_t n,
+                void* dL_din_f16, float* grad_weights, float grad_scale, rnb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

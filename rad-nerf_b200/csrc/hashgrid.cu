@@ -1,0 +1,271 @@
+// hashgrid.cu -- multiresolution hash-grid encoding (forward gather, backward scatter-add)
+// and degree-4 spherical harmonics for sm_100a.
+//
+// Replaces tinycudann's Encoding{Grid/Hash} / Encoding{SphericalHarmonics} as the reference
+// configures them (models/networks.py:42-55, 70-77, 234-256).  tinycudann is not vendored in
+// the reference; the algorithm restated here is its published one (see oracle/tcnn_cpu.py).
+//
+// B200 layout decisions:
+//  * one THREAD per sample loops over all L levels: xyz is read once, the L*F = 32 fp16
+//    features of a sample are produced in registers and written as one 64 B row (4 x 16 B
+//    stores; a warp writes 2 KiB contiguous).  The 16 x 8 gathers of a thread are independent,
+//    so each thread keeps dozens of 4 B loads in flight (latency hiding without occupancy);
+//  * the fp16 table (22-26 MB) is L2-resident on B200 (126 MB L2); the dense coarse levels
+//    (16^3 .. 64^3 entries) are additionally L1-resident through the read-only path
+//    (consecutive threads = consecutive samples of one ray = same / adjacent coarse cells);
+//  * backward: fp32 gradient table updated with 8-byte vector reductions
+//    (red.global.add.v2.f32, one per corner for both features); on the dense coarse levels
+//    runs of lanes that hit the same entry are first combined with a segmented warp reduction
+//    so that one lane issues the reduction (warp-level atomics aggregation).
+#include "common.cuh"
+
+namespace rnb {
+
+struct GridLevels {
+  int n_levels;
+  float scale[RNB_MAX_LEVELS];
+  uint32_t res[RNB_MAX_LEVELS];
+  uint32_t offset[RNB_MAX_LEVELS + 1];
+};
+
+__device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, uint32_t res, uint32_t size, bool dense) {
+  uint32_t idx;
+  if (dense) {
+    idx = x + y * res + z * res * res;
+    if (idx >= size) idx %= size;   // only the +1 corner on the upper boundary can leave the level
+  } else {
+    idx = x ^ (y * 2654435761u) ^ (z * 805459861u);
+    idx = ((size & (size - 1u)) == 0u) ? (idx & (size - 1u)) : (idx % size);
+  }
+  return idx;
+}
+
+// tcnn grid_index(): the dense index is accumulated while stride <= size; the level is hashed iff
+// the full dense grid does not fit (size < res^3).
+__device__ __forceinline__ bool level_is_dense(uint32_t res, uint32_t size) {
+  return (uint64_t)res * res * res <= (uint64_t)size;
+}
+
+struct Corner {
+  uint32_t cx, cy, cz;
+  float wx, wy, wz;
+};
+
+__device__ __forceinline__ Corner locate(float x, float y, float z, float scale) {
+  Corner c;
+  const float px = fmaf(scale, x, 0.5f), py = fmaf(scale, y, 0.5f), pz = fmaf(scale, z, 0.5f);
+  const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+  c.cx = (uint32_t)(int)fx; c.cy = (uint32_t)(int)fy; c.cz = (uint32_t)(int)fz;
+  c.wx = px - fx; c.wy = py - fy; c.wz = pz - fz;
+  return c;
+}
+
+__global__ void __launch_bounds__(128) hashgrid_fwd_kernel(const float* __restrict__ xs, int64_t n,
+                                                           const __half2* __restrict__ table, GridLevels g,
+                                                           __half2* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float x = ld_stream_f32(xs + 3 * i), y = ld_stream_f32(xs + 3 * i + 1), z = ld_stream_f32(xs + 3 * i + 2);
+  __half2* o = out + i * g.n_levels;
+  for (int l0 = 0; l0 < g.n_levels; l0 += 4) {
+    uint32_t packed[4];
+#pragma unroll
+    for (int dl = 0; dl < 4; dl++) {
+      const int l = l0 + dl;
+      if (l < g.n_levels) {
+        const uint32_t res = g.res[l], off = g.offset[l], size = g.offset[l + 1] - off;
+        const bool dense = level_is_dense(res, size);
+        const Corner c = locate(x, y, z, g.scale[l]);
+        const __half2* t = table + off;
+        __half2 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const uint32_t idx = grid_index(c.cx + (k & 1), c.cy + ((k >> 1) & 1), c.cz + (k >> 2), res, size, dense);
+          v[k] = __ldg(t + idx);
+        }
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const float w = ((k & 1) ? c.wx : 1.f - c.wx) * (((k >> 1) & 1) ? c.wy : 1.f - c.wy) * ((k >> 2) ? c.wz : 1.f - c.wz);
+          const float2 f = __half22float2(v[k]);
+          a0 = fmaf(w, f.x, a0); a1 = fmaf(w, f.y, a1);
+        }
+        const __half2 h = __floats2half2_rn(a0, a1);
+        packed[dl] = *reinterpret_cast<const uint32_t*>(&h);
+      } else {
+        packed[dl] = 0u;
+      }
+    }
+    if (l0 + 4 <= g.n_levels) {
+      *reinterpret_cast<uint4*>(o + l0) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    } else {
+      for (int dl = 0; l0 + dl < g.n_levels; dl++) *reinterpret_cast<uint32_t*>(o + l0 + dl) = packed[dl];
+    }
+  }
+}
+
+__device__ __forceinline__ void red_add_f32x2(float* addr, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
+}
+
+// Warp-aggregated scatter.  Consecutive lanes are consecutive samples of one ray, so lanes
+// that hit the same coarse entry form RUNS: a segmented warp reduction over runs of equal index
+// (5 shuffle steps) leaves the run total in the run's first lane, which issues one reduction.
+__device__ __forceinline__ void scatter_aggregated(float* grad_level, uint32_t idx, float g0, float g1, bool active) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t key = active ? idx : 0xffffffffu;
+  const uint32_t prev = __shfl_up_sync(kFullMask, key, 1);
+  const unsigned heads = __ballot_sync(kFullMask, lane == 0 || prev != key);
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const float v0 = __shfl_down_sync(kFullMask, g0, o), v1 = __shfl_down_sync(kFullMask, g1, o);
+    // lane+o belongs to my run iff no run head lies in (lane, lane+o]
+    const unsigned between = ((heads >> lane) >> 1) & ((1u << o) - 1u);
+    if (lane + o < 32 && between == 0u) { g0 += v0; g1 += v1; }
+  }
+  if (active && ((heads >> lane) & 1u)) red_add_f32x2(grad_level + 2 * (size_t)idx, g0, g1);
+}
+
+__global__ void __launch_bounds__(128) hashgrid_bwd_kernel(const float* __restrict__ xs, int64_t n,
+                                                           const __half2* __restrict__ dy, GridLevels g,
+                                                           float grad_scale, float* __restrict__ grad,
+                                                           int n_aggregate_levels) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = i < n;
+  float x = 0.f, y = 0.f, z = 0.f;
+  if (active) { x = ld_stream_f32(xs + 3 * i); y = ld_stream_f32(xs + 3 * i + 1); z = ld_stream_f32(xs + 3 * i + 2); }
+  for (int l = 0; l < g.n_levels; l++) {
+    const uint32_t res = g.res[l], off = g.offset[l], size = g.offset[l + 1] - off;
+    const bool dense = level_is_dense(res, size);
+    const Corner c = locate(x, y, z, g.scale[l]);
+    float2 d = make_float2(0.f, 0.f);
+    if (active) {
+      d = __half22float2(dy[i * g.n_levels + l]);
+      d.x *= grad_scale; d.y *= grad_scale;
+    }
+    float* gl = grad + 2 * (size_t)off;
+    const bool aggregate = l < n_aggregate_levels;   // warp-uniform
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint32_t idx = grid_index(c.cx + (k & 1), c.cy + ((k >> 1) & 1), c.cz + (k >> 2), res, size, dense);
+      const float w = ((k & 1) ? c.wx : 1.f - c.wx) * (((k >> 1) & 1) ? c.wy : 1.f - c.wy) * ((k >> 2) ? c.wz : 1.f - c.wz);
+      if (aggregate) {
+        scatter_aggregated(gl, idx, w * d.x, w * d.y, active);
+      } else if (active) {
+        red_add_f32x2(gl + 2 * (size_t)idx, w * d.x, w * d.y);
+      }
+    }
+  }
+}
+
+// tcnn SphericalHarmonics degree 4: u in [0,1]^3 -> d = 2u-1 -> 16 real SH basis values (fp16).
+__global__ void __launch_bounds__(256) sh4_fwd_kernel(const float* __restrict__ u, int64_t n, __half* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float x = u[3 * i] * 2.f - 1.f, y = u[3 * i + 1] * 2.f - 1.f, z = u[3 * i + 2] * 2.f - 1.f;
+  const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+  float o[16];
+  o[0] = 0.28209479177387814f;
+  o[1] = -0.48860251190291987f * y;
+  o[2] = 0.48860251190291987f * z;
+  o[3] = -0.48860251190291987f * x;
+  o[4] = 1.0925484305920792f * xy;
+  o[5] = -1.0925484305920792f * yz;
+  o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+  o[7] = -1.0925484305920792f * xz;
+  o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
+  o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+  o[10] = 2.8906114426405538f * xy * z;
+  o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
+  o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
+  o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+  o[14] = 1.4453057213202769f * z * (x2 - y2);
+  o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+  uint32_t p[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) { const __half2 h = __floats2half2_rn(o[2 * k], o[2 * k + 1]); p[k] = *reinterpret_cast<const uint32_t*>(&h); }
+  uint4* dst = reinterpret_cast<uint4*>(out + i * 16);
+  dst[0] = make_uint4(p[0], p[1], p[2], p[3]);
+  dst[1] = make_uint4(p[4], p[5], p[6], p[7]);
+}
+
+__global__ void __launch_bounds__(256) cast_f32_f16_kernel(const float* __restrict__ src, int64_t n, __half* __restrict__ dst) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n4 = n >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 v = ld_stream_f32x4(reinterpret_cast<const float4*>(src) + i);
+    const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+    reinterpret_cast<uint2*>(dst)[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+  }
+  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = __float2half_rn(src[i]);
+}
+
+static int to_levels(const rnb_grid_meta* m, GridLevels* g, const char* what) {
+  RNB_REQUIRE(m != nullptr, what);
+  RNB_REQUIRE(m->n_levels >= 1 && m->n_levels <= RNB_MAX_LEVELS && m->n_features == 2, what);
+  g->n_levels = m->n_levels;
+  for (int l = 0; l < m->n_levels; l++) {
+    g->scale[l] = m->scale[l]; g->res[l] = m->res[l]; g->offset[l] = m->offset[l];
+    RNB_REQUIRE(m->offset[l + 1] > m->offset[l] && m->res[l] >= 2, what);
+  }
+  g->offset[m->n_levels] = m->offset[m->n_levels];
+  return RNB_OK;
+}
+
+}  // namespace rnb
+
+using namespace rnb;
+
+extern "C" {
+
+int rnb_hashgrid_fwd(const float* x, int64_t n, const void* table_f16, const rnb_grid_meta* meta, void* out_f16,
+                     rnb_stream_t stream) {
+  const char* what = "rnb_hashgrid_fwd";
+  RNB_REQUIRE(n >= 0, what);
+  GridLevels g;
+  if (int rc = to_levels(meta, &g, what)) return rc;
+  if (n == 0) return RNB_OK;
+  RNB_REQUIRE(x && table_f16 && out_f16, what);
+  RNB_REQUIRE(((uintptr_t)out_f16 & 15) == 0 || (g.n_levels & 3) != 0, what);
+  hashgrid_fwd_kernel<<<ceil_div(n, 128), 128, 0, as_stream(stream)>>>(x, n, (const __half2*)table_f16, g, (__half2*)out_f16);
+  return check_launch(what);
+}
+
+int rnb_hashgrid_bwd(const float* x, int64_t n, const void* dL_dout_f16, const rnb_grid_meta* meta, float grad_scale,
+                     float* grad_table, rnb_stream_t stream) {
+  const char* what = "rnb_hashgrid_bwd";
+  RNB_REQUIRE(n >= 0, what);
+  GridLevels g;
+  if (int rc = to_levels(meta, &g, what)) return rc;
+  if (n == 0) return RNB_OK;
+  RNB_REQUIRE(x && dL_dout_f16 && grad_table, what);
+  // aggregate duplicates on the dense levels whose cells are coarser than a marching step run
+  int n_agg = 0;
+  for (int l = 0; l < g.n_levels; l++)
+    if ((uint64_t)g.res[l] * g.res[l] * g.res[l] <= (uint64_t)(g.offset[l + 1] - g.offset[l]) && g.res[l] <= 64) n_agg = l + 1;
+  hashgrid_bwd_kernel<<<ceil_div(n, 128), 128, 0, as_stream(stream)>>>(x, n, (const __half2*)dL_dout_f16, g, grad_scale, grad_table, n_agg);
+  return check_launch(what);
+}
+
+int rnb_sh4_fwd(const float* u, int64_t n, void* out_f16, rnb_stream_t stream) {
+  const char* what = "rnb_sh4_fwd";
+  RNB_REQUIRE(n >= 0, what);
+  if (n == 0) return RNB_OK;
+  RNB_REQUIRE(u && out_f16, what);
+  sh4_fwd_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(u, n, (__half*)out_f16);
+  return check_launch(what);
+}
+
+int rnb_cast_f32_to_f16(const float* src, int64_t n, void* dst_f16, rnb_stream_t stream) {
+  const char* what = "rnb_cast_f32_to_f16";
+  RNB_REQUIRE(n >= 0, what);
+  if (n == 0) return RNB_OK;
+  RNB_REQUIRE(src && dst_f16, what);
+  int64_t blocks = (n / 4 + 255) / 256;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  if (blocks < 1) blocks = 1;
+  cast_f32_f16_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(src, n, (__half*)dst_f16);
+  return check_launch(what);
+}
+
+}  // extern "C"

@@ -108,6 +108,7 @@ __global__ void __launch_bounds__(128) march_test_kernel(
   float t = hits_t[2 * r];
   const float t2 = hits_t[2 * r + 1];
   int k = 0; Probe s;
+  float t_resume = t;
   const int64_t o0 = n * N_samples;
   while (t < t2 && k < N_samples) {
     if (march_probe(ray, p, t, s)) {
@@ -116,9 +117,10 @@ __global__ void __launch_bounds__(128) march_test_kernel(
       dirs[3 * o] = ray.dx; dirs[3 * o + 1] = ray.dy; dirs[3 * o + 2] = ray.dz;
       ts[o] = t; deltas[o] = s.dt;
       t = __fadd_rn(t, s.dt); k++;
+      t_resume = t;  // only a taken sample moves the resume point (raymarching.cu:389-391)
     }
   }
-  if (k > 0) hits_t[2 * r] = t;  // resume point (raymarching.cu:389-391)
+  if (k > 0) hits_t[2 * r] = t_resume;
   n_eff[n] = k;
   for (int j = k; j < N_samples; j++) {
     const int64_t o = o0 + j;
