@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py -- Rad-NeRF hot-path benchmark on B200 (contract: see the task statement).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --steps K --warmup W    # the reference's math on host cores
+
+Metric (BASELINE.json): train rays/s for Rad-NeRF K=2 (config "radnerf_tat_k2": TAT-shape
+1920x1080 cameras, scale 0.5, batch 8192 rays per GPU, lambda_dm=5e-3, lambda_cv=1e-2,
+lambda_opacity=1e-3), synthetic analytic scene, tinycudann-style random init.  One "step" =
+the training step of train_ml.py:172-200 (grid update every 16 steps, gate, K x (march, field,
+composite), NeRFLoss, backward, gradient all-reduce when N>1, Adam).  Weak scaling: every rank
+gets its own 8192-ray batch.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BATCH = 8192
+N_BATCHES = 8          # distinct pre-generated batches cycled through
+
+
+def workload(name):
+    import radnerf_b200  # noqa: F401
+    from radnerf_b200 import synthetic as syn
+    w = dict(syn.WORKLOADS[name])
+    return syn, w
+
+
+def make_batches(syn, w, rank, n_batches=N_BATCHES, batch=BATCH):
+    cam = syn.make_cameras(100, w["radius"], w["H"], w["W"], w["fx"])
+    scene = syn.make_scene(w["scale"], 1234)
+    out = []
+    for b in range(n_batches):
+        o, d, _, _ = syn.train_batch(cam, batch, seed=42 + 1000 * rank + b)
+        # target colours: the analytic scene's colour at the ray's box midpoint (cheap stand-in for images)
+        tgt = scene.color(o + d * 1.5)
+        out.append((o, d, tgt.astype(np.float32)))
+    return out
+
+
+def scene_bitfields(syn, w):
+    bfs = []
+    for i in range(w["K"]):
+        sc = syn.make_scene(w["scale"], 1234, jitter_seed=i if i else None)
+        bfs.append(syn.packbits_np(sc.density_grid, sc.threshold))
+    return bfs
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for r in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons, "samples": len(rows)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1400.0, "fallback"
+
+
+# algorithmic HBM bytes of one launch of each entry point, as a function of the
+# samples N / rays R it processed
+ALGO_BYTES = {
+    "rnb_hashgrid_fwd": lambda N, R: 76 * N,
+    "rnb_hashgrid_bwd": lambda N, R: 76 * N,
+    "rnb_composite_train_fw": lambda N, R: 28 * N + 52 * R,
+    "rnb_composite_train_bw": lambda N, R: 48 * N + 64 * R,
+    "rnb_raymarching_train_write": lambda N, R: 32 * N + 60 * R,
+    "rnb_raymarching_train_count": lambda N, R: 60 * R,
+}
+ALGO_FLOPS = {  # MLP flops per row as executed (padded), fwd / bwd(dgrad+wgrad)
+    "rnb_mlp_fwd": 2 * (32 * 64 + 64 * 32),
+    "rnb_mlp_bwd": 4 * (32 * 64 + 64 * 32),
+}
+
+
+def run_reference(args):
+    """The reference's math for the same step, in plain PyTorch + the C restatement of its kernels,
+    on the host cores (the reference itself has no CPU implementation of this path)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    syn, w = workload(args.workload)
+    from oracle import render_cpu as R
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    K = w["K"]
+    bfs = scene_bitfields(syn, w)
+    P = R.FieldParams(w["scale"], K, seed=0).requires_grad_(True)
+    opt = torch.optim.Adam(list(P.p.values()), 1e-2, eps=1e-15)
+    esf = syn.exp_step_factor_for_scale(w["scale"])
+    C = syn.cascades_for_scale(w["scale"])
+    batches = make_batches(syn, w, 0, n_batches=2)
+    rng = np.random.RandomState(7)
+
+    def step(n):
+        o, d, t = (a[:n] for a in batches[step.i % 2]); step.i += 1
+        noises = [rng.rand(n).astype(np.float32) for _ in range(K)]
+        res = R.ml_render_train(P, o, d, bfs, noises, C, esf)
+        loss, _ = R.nerf_loss(res, torch.from_numpy(t), 1e-3, 1e-2 if K > 1 else 0, 5e-3 if K > 1 else 0)
+        opt.zero_grad(); loss.backward(); opt.step()
+        return float(loss)
+    step.i = 0
+    t0 = time.time(); step(128); probe = time.time() - t0
+    budget = 90.0   # seconds for warmup + timed steps
+    n = int(max(64, min(BATCH, 128 * budget / max(probe, 1e-3) / (args.steps + args.warmup))))
+    n = n // 64 * 64
+    for _ in range(args.warmup):
+        step(n)
+    t0 = time.time()
+    for _ in range(args.steps):
+        step(n)
+    dt = time.time() - t0
+    val = n * args.steps / dt
+    sample = f"{n} of {BATCH} rays per step (same scene/cameras/K), fwd+loss+bwd+Adam"
+    line = {"impl": "reference", "metric": "train_rays_per_s", "value": val, "unit": "rays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp16 rounding points)", "data": "synthetic",
+            "config": {"workload": args.workload, "K": K, "scale": w["scale"], "batch_rays_per_gpu": BATCH,
+                       "params": "tcnn-style random init", "occupancy": "analytic scene, fixed"},
+            "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_product(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    syn, w = workload(args.workload)
+    from radnerf_b200 import _lib
+    from radnerf_b200.trainer import Trainer
+    _lib.lib()   # fail loudly if the CUDA library is missing: there is no fallback
+    K = w["K"]
+    tr = Trainer(scale=w["scale"], K=K, freeze_occupancy=True, device=f"cuda:{local}")
+    tr.set_occupancy(scene_bitfields(syn, w))
+    host = [tuple(torch.from_numpy(a).pin_memory() for a in b) for b in make_batches(syn, w, rank)]
+    dev = [tuple(a.cuda(non_blocking=True) for a in b) for b in host]
+    flush = torch.empty(256 * 1024 * 1024 // 4, device="cuda")      # 256 MiB > 126 MB L2
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        sync_all()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s in range(steps):
+            fn(s)
+        e1.record()
+        sync_all()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    def dev_step(s):
+        flush.add_(1.0)     # evict L2 between steps (inputs are smaller than L2)
+        tr.step(*dev[s % len(dev)])
+
+    losses = []
+
+    def e2e_step(s):
+        flush.add_(1.0)
+        o, d, t = (a.cuda(non_blocking=True) for a in host[s % len(host)])
+        losses.append(float(tr.step(o, d, t)))      # device->host read of the step's loss
+
+    for s in range(args.warmup):
+        dev_step(s)
+    # time the L2 flush alone so that it can be subtracted (it is not part of the step)
+    flush_ms = timed(lambda s: flush.add_(1.0), args.steps) / args.steps
+    clocks = ClockSampler(local); clocks.start()
+    n0 = _lib.launch_count
+    _lib.profile_begin()
+    ms = timed(dev_step, args.steps)
+    prof = _lib.profile_end()
+    launches = _lib.launch_count - n0
+    clk = clocks.stop()
+    ms_step = ms / args.steps - flush_ms
+    e2e_ms = timed(e2e_step, args.steps) / args.steps - flush_ms
+    rays_total = BATCH * world
+    value = rays_total / (ms_step * 1e-3)
+    e2e_val = rays_total / (e2e_ms * 1e-3)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # samples per sub-NeRF pass (for the algorithmic-bytes figures)
+    res = tr.last_results
+    hbm, tflops, which = measured_peaks()
+    kern = sorted(((t, n, c) for n, (c, t) in prof.items()), reverse=True)
+    total_kernel_ms = sum(t for t, _, _ in kern)
+    # average samples per field pass, measured from the marcher's own counters
+    from radnerf_b200 import vren
+    import torch as _t
+    o, d, _ = dev[0]
+    from radnerf_b200.models._render_core import intersect_scene_box
+    hits = intersect_scene_box(tr.model, o, d)[:, 0].contiguous()
+    Ns = []
+    for i in range(K):
+        bf = getattr(tr.model, "density_bitfield" if K == 1 else f"density_bitfield_{i}")
+        out = vren.raymarching_train(o, d, hits, bf, tr.model.cascades, w["scale"], tr.exp_step_factor,
+                                     _t.rand(BATCH, device="cuda"), 128, 1024)
+        Ns.append(int(out[5][0]))
+    N_avg = float(np.mean(Ns))
+    top_t, top_name, top_calls = kern[0]
+    per_launch_ms = top_t / top_calls
+    if top_name in ALGO_FLOPS:
+        achieved = ALGO_FLOPS[top_name] * N_avg / (per_launch_ms * 1e-3) / 1e12
+        roof = {"kernel": top_name, "bound": "tensor", "achieved": achieved, "peak": tflops, "unit": "TFLOP/s",
+                "frac": achieved / tflops, "traffic": None, "peak_source": which}
+    else:
+        f = ALGO_BYTES.get(top_name, lambda N, R: 0)
+        achieved = f(N_avg, BATCH) / (per_launch_ms * 1e-3) / 1e9
+        roof = {"kernel": top_name, "bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s",
+                "frac": achieved / hbm, "traffic": None, "peak_source": which}
+    roof["share_of_step"] = top_t / args.steps / ms_step
+    roof["kernel_ms_per_step"] = {n: round(t / args.steps, 4) for t, n, _ in kern}
+    roof["our_kernels_share_of_step"] = total_kernel_ms / args.steps / ms_step
+    line = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16 (fp32 accumulate; fp32 march/composite)", "data": "synthetic",
+            "config": {"workload": args.workload, "K": K, "scale": w["scale"], "batch_rays_per_gpu": BATCH,
+                       "samples_per_ray": N_avg / BATCH, "params": "tcnn-style random init",
+                       "occupancy": "analytic scene, fixed; grid update every 16 steps runs on shadow grids",
+                       "l2": "flushed between steps (256 MiB write, its time subtracted)", "parallelism": f"ray-sharded dp{world}"},
+            "clocks": clk,
+            "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * BATCH * 12, "d2h_bytes_per_step": 4,
+                    "ms_per_step": e2e_ms},
+            "gpu_launches": launches, "roofline": roof, "final_loss": losses[-1] if losses else None}
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args):
+    """Oracle (CPU port of the reference's math) on a bounded sample of the same workload."""
+    import subprocess as sp
+    out = sp.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                  "--workload", args.workload], capture_output=True, text=True, timeout=600)
+    for ln in out.stdout.splitlines()[::-1]:
+        if ln.startswith("{"):
+            return json.loads(ln)["cpu_baseline"]
+    return {"value": None, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: " + out.stderr[-200:]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="radnerf_tat_k2")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_product(args)
+
+
+if __name__ == "__main__":
+    main()

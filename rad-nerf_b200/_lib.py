@@ -72,10 +72,43 @@ def stream_arg(device=None):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+# kernels launched per C-ABI call (for bench.py's `gpu_launches` claim)
+KERNELS_PER_CALL = {"rnb_raymarching_train_count": 2}
+launch_count = 0
+_prof = None
+
+
+def profile_begin():
+    """Start recording a CUDA-event pair around every C-ABI call (bench.py roofline leg)."""
+    global _prof
+    _prof = []
+
+
+def profile_end():
+    """-> {entry point: (calls, total_ms)} for the calls since profile_begin()."""
+    global _prof
+    rec, _prof = _prof, None
+    torch.cuda.synchronize()
+    out = {}
+    for name, e0, e1 in rec or []:
+        c, t = out.get(name, (0, 0.0))
+        out[name] = (c + 1, t + e0.elapsed_time(e1))
+    return out
+
+
 def call(name: str, *args):
     """Call `rnb_<name>`; raises RadNerfB200Error with the library's message on failure."""
+    global launch_count
     fn = getattr(lib(), name)
-    rc = fn(*[_arg(a) for a in args])
+    launch_count += KERNELS_PER_CALL.get(name, 1)
+    if _prof is not None:
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*[_arg(a) for a in args])
+        e1.record()
+        _prof.append((name, e0, e1))
+    else:
+        rc = fn(*[_arg(a) for a in args])
     if rc != 0:
         msg = lib().rnb_last_error()
         raise RadNerfB200Error(f"{name} failed ({rc}): {msg.decode() if msg else ''}")

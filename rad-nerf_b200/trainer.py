@@ -1,0 +1,119 @@
+"""Lightning-free training driver for the Rad-NeRF hot path: one
+process per GPU, the step of train_ml.py:172-200 --
+
+    every 16 steps: update_density_grid            (train_ml.py:173-177)
+    ml_render(model, gate, rays_o, rays_d)         (ml_rendering.py:11-78)
+    NeRFLoss: rgb + opacity + cv_importance + depth_mutual, loss = sum of term means
+    backward -> [all-reduce of the flat gradient bucket over NCCL when world_size > 1] -> Adam(eps=1e-15)
+
+Rays shard naturally: with world_size W each rank renders its own slice of the global batch;
+the only exchange is one all-reduce (sum) of the gradients, plus the K-float gating importance
+before the (non-linear) CV loss.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import synthetic as syn
+from .losses import NeRFLoss
+from .models.ml_rendering import ml_render
+from .models.networks import MNGP, NGP, Ray_Gate
+from .models.rendering import render
+
+
+class Trainer:
+    def __init__(self, scale=0.5, K=2, lr=1e-2, log2_T=19, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
+                 loss_scale=1024.0, device="cuda", update_interval=16, warmup_steps=256, freeze_occupancy=False,
+                 random_bg=False, seed=0):
+        self.device = torch.device(device)
+        self.K, self.scale = K, scale
+        self.exp_step_factor = syn.exp_step_factor_for_scale(scale)
+        torch.manual_seed(seed)
+        if K == 1:
+            self.model = NGP(scale, t=log2_T).to(self.device)
+            self.gate = None
+        else:
+            self.model = MNGP(scale, size=K, t=log2_T).to(self.device)
+            self.gate = Ray_Gate(K).to(self.device)
+        self.params = [p for p in list(self.model.parameters()) + (list(self.gate.parameters()) if self.gate else [])
+                       if p.numel() > 0]
+        self.opt = torch.optim.Adam(self.params, lr, eps=1e-15, fused=True)   # FusedAdam(lr, eps=1e-15), train_ml.py:143
+        self.loss_fn = NeRFLoss()
+        self.lam = dict(lambda_opacity=lambda_opacity, lambda_cv_importance=lambda_cv if K > 1 else 0,
+                        lambda_depth_mutual=lambda_dm if K > 1 else 0)
+        self.loss_scale = loss_scale
+        self.update_interval, self.warmup_steps = update_interval, warmup_steps
+        self.freeze_occupancy = freeze_occupancy
+        self.random_bg = random_bg
+        self.global_step = 0
+        self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        self._shadow = None
+
+    # -- occupancy ---------------------------------------------------------------------------
+    def set_occupancy(self, bitfields):
+        """Install externally computed bitfields (e.g. the synthetic scenes of bench.py)."""
+        for i, bf in enumerate(bitfields):
+            name = "density_bitfield" if self.K == 1 else f"density_bitfield_{i}"
+            getattr(self.model, name).copy_(torch.as_tensor(bf, device=self.device))
+
+    def _grid_update(self):
+        thr = syn.DENSITY_THRESHOLD
+        warm = self.global_step < self.warmup_steps
+        if not self.freeze_occupancy:
+            self.model.update_density_grid(thr, warmup=warm)
+            return
+        # Benchmark mode: the SAME work (cell sampling, density evaluation, EMA-max, mean, packbits)
+        # runs against shadow buffers so that the occupancy used for marching -- and therefore the
+        # number of samples per ray -- stays that of the synthetic scene.
+        names = ["density_grid", "density_bitfield"] if self.K == 1 else \
+            [f"density_{k}_{i}" for i in range(self.K) for k in ("grid", "bitfield")]
+        keep = {n: getattr(self.model, n) for n in names}
+        if self._shadow is None:
+            self._shadow = {n: torch.zeros_like(v) for n, v in keep.items()}
+        for n, v in self._shadow.items():
+            setattr(self.model, n, v)
+        self.model.update_density_grid(thr, warmup=warm)
+        for n in names:
+            self._shadow[n] = getattr(self.model, n)
+            setattr(self.model, n, keep[n])
+
+    # -- one step ----------------------------------------------------------------------------
+    def step(self, rays_o, rays_d, target_rgb):
+        """rays_o, rays_d, target_rgb: (B_local,3) fp32 CUDA tensors.  Returns the (unscaled) loss tensor."""
+        if self.global_step % self.update_interval == 0:
+            self._grid_update()
+        kw = dict(test_time=False, random_bg=self.random_bg)
+        if self.exp_step_factor:
+            kw["exp_step_factor"] = self.exp_step_factor
+        if self.K == 1:
+            results = render(self.model, rays_o, rays_d, **kw)
+        else:
+            results = ml_render(self.model, self.gate, rays_o, rays_d, rays_d, **kw)
+            if self.world > 1:   # CV loss is non-linear in the batch: importance must be global (8e)
+                imp = results["gating_importance"]
+                tot = imp.detach().clone()
+                dist.all_reduce(tot)
+                results["gating_importance"] = imp + (tot - imp.detach())
+        loss_d = self.loss_fn(results, {"rgb": target_rgb}, **self.lam)
+        if self.world > 1 and "cv_importance" in loss_d:
+            # the CV term is one GLOBAL scalar: its per-rank gradient pieces must be SUMMED, while the
+            # gradient all-reduce below averages -- pre-multiply by the world size
+            loss_d["cv_importance"] = loss_d["cv_importance"] * self.world
+        loss = sum(v.mean() for v in loss_d.values())
+        self.opt.zero_grad(set_to_none=True)
+        (loss * self.loss_scale).backward()
+        if self.world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in self.params])
+            dist.all_reduce(flat)          # one flat bucket over NCCL / NVLink
+            flat.mul_(1.0 / (self.world * self.loss_scale))
+            o = 0
+            for p in self.params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
+        else:
+            for p in self.params:
+                p.grad.mul_(1.0 / self.loss_scale)
+        self.opt.step()
+        self.global_step += 1
+        self.last_results = results
+        return loss.detach()
