@@ -76,24 +76,27 @@ int rnb_packbits_devthr(const float* density_grid, int64_t n_bytes, const float*
  * ------------------------------------------------------------------------------------ */
 
 /* binding.cpp:60-81 -> raymarching.cu:166-332, split in two phases so that the caller owns
- * the data-dependent allocation.  Phase 1 marches every ray once, and writes
+ * the data-dependent allocation.  Phase 1 marches every ray ONCE (warp per ray) and writes
  *   rays_a (n_rays,3) i64 = [ray_idx, start_idx, N_samples] in ASCENDING RAY ORDER with
  *   start_idx = exclusive prefix sum of N_samples (a deterministic, legal outcome of the
- *   reference's atomicAdd slot reservation, raymarching.cu:237-241), and
- *   counter (2) i32 = [total_samples, n_rays]   (the reference's `counter`).
+ *   reference's atomicAdd slot reservation, raymarching.cu:237-241),
+ *   counter (2) i32 = [total_samples, n_rays]   (the reference's `counter`), and
+ *   t_scratch (n_rays*max_samples) f32: t of sample k of ray r at [r*max_samples + k]
+ *   (only the first N_samples entries of a row are written; no initialisation needed).
  * hits_t is (n_rays,2) f32 (t1 = -1 for a miss); noise (n_rays) f32 in [0,1). */
 int rnb_raymarching_train_count(const float* rays_o, const float* rays_d, const float* hits_t,
                                 const uint8_t* density_bitfield, int cascades, float scale,
                                 float exp_step_factor, const float* noise, int grid_size,
                                 int max_samples, int64_t n_rays,
-                                int64_t* rays_a, int32_t* counter, rnb_stream_t stream);
-/* Phase 2: re-march and write xyzs, dirs (cap,3) f32 and deltas, ts (cap) f32 for the
- * samples whose slot is < cap (cap >= counter[0] gives the reference result). */
-int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, const float* hits_t,
-                                const uint8_t* density_bitfield, int cascades, float scale,
-                                float exp_step_factor, const float* noise, int grid_size,
-                                int max_samples, int64_t n_rays, const int64_t* rays_a, int64_t cap,
-                                float* xyzs, float* dirs, float* deltas, float* ts,
+                                int64_t* rays_a, int32_t* counter, float* t_scratch,
+                                rnb_stream_t stream);
+/* Phase 2: expands t_scratch into xyzs, dirs (cap,3) f32 and deltas, ts (cap) f32 for the
+ * samples whose slot is < cap (cap >= counter[0] gives the reference result); the payload is
+ * bit-identical to the reference's second march (x = o + t*d as one FMA, dt = calc_dt(t)). */
+int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, float scale,
+                                float exp_step_factor, int grid_size, int max_samples,
+                                int64_t n_rays, const int64_t* rays_a, const float* t_scratch,
+                                int64_t cap, float* xyzs, float* dirs, float* deltas, float* ts,
                                 rnb_stream_t stream);
 
 /* binding.cpp:84-106 -> raymarching.cu:335-454.  hits_t (n_rays_total,2) f32 is MUTATED

@@ -1,26 +1,27 @@
 // march.cu -- training / test-time occupancy-grid marchers (replaces raymarching.cu:166-454).
-#include "march.cuh"
+#include "march_warp.cuh"
 
 namespace rnb {
 
-// ---- training: phase 1 (count) ---------------------------------------------------------
-// One thread per ray; 64-thread CTAs so that a training batch of 8192 rays spreads over
-// 128 of the 148 SMs (the loop is latency-bound: one dependent bitfield load per step).
-// Writes the per-ray count into rays_a[r][2]; the scan kernel below completes the rows.
-__global__ void __launch_bounds__(64) march_train_count_kernel(
+// ---- training: phase 1 (march once) ------------------------------------------------------
+// Warp per ray (march_warp.cuh); 8 rays per 256-thread CTA.  Writes the per-ray count into
+// rays_a[r][2] (the scan kernel below completes the rows) and the t of every sample into
+// t_scratch[r * max_samples + k], so that phase 2 is a pure streaming expansion (no re-march).
+template <bool kConstDt>
+__global__ void __launch_bounds__(256) march_train_count_kernel(
     const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ hits_t,
-    const float* __restrict__ noise, MarchParams p, int64_t n_rays, int64_t* __restrict__ rays_a) {
-  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const float* __restrict__ noise, MarchParams p, int64_t n_rays, int64_t* __restrict__ rays_a,
+    float* __restrict__ t_scratch) {
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (r >= n_rays) return;
   const Ray ray = load_ray(rays_o, rays_d, r);
   float t1 = __ldg(hits_t + 2 * r);
   const float t2 = __ldg(hits_t + 2 * r + 1);
   if (t1 >= 0) t1 = __fmaf_rn(calc_dt(t1, p), __ldg(noise + r), t1);  // raymarching.cu:195-198
-  float t = t1; int n = 0; Probe s;
-  while (0 <= t && t < t2 && n < p.max_samples) {
-    if (march_probe(ray, p, t, s)) { t = __fadd_rn(t, s.dt); n++; }
-  }
-  rays_a[3 * r + 2] = n;
+  float t_next;
+  const int n = march_ray_warp<kConstDt>(ray, p, p.bitfield, t1, t2, p.max_samples,
+                                         t_scratch + r * (int64_t)p.max_samples, t_next);
+  if ((threadIdx.x & 31) == 0) rays_a[3 * r + 2] = n;
 }
 
 // ---- training: exclusive scan of the counts -> rays_a rows + counter --------------------
@@ -64,69 +65,71 @@ __global__ void __launch_bounds__(1024) march_train_scan_kernel(int64_t n_rays, 
   if (tid == 0) { counter[0] = carry_s; counter[1] = (int32_t)n_rays; }
 }
 
-// ---- training: phase 2 (write) -----------------------------------------------------------
-__global__ void __launch_bounds__(64) march_train_write_kernel(
-    const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ hits_t,
-    const float* __restrict__ noise, MarchParams p, int64_t n_rays, const int64_t* __restrict__ rays_a,
-    int64_t cap, float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas,
-    float* __restrict__ ts) {
-  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// ---- training: phase 2 (expand) ----------------------------------------------------------
+// Warp per ray: sample k of ray r is t = t_scratch[r*max_samples + k]; position and step are
+// recomputed with the marcher's own expressions (x = fma(d, t, o), dt = calc_dt(t)), so the
+// payload is bit-identical to what the reference writes in its second march.  Lane-contiguous
+// (coalesced) stores; nothing is memset.
+__global__ void __launch_bounds__(256) march_train_write_kernel(
+    const float* __restrict__ rays_o, const float* __restrict__ rays_d, MarchParams p, int64_t n_rays,
+    const int64_t* __restrict__ rays_a, const float* __restrict__ t_scratch, int64_t cap,
+    float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas, float* __restrict__ ts) {
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (r >= n_rays) return;
   const int64_t start = rays_a[3 * r + 1];
   const int n_samples = (int)rays_a[3 * r + 2];
   if (n_samples == 0) return;
   const Ray ray = load_ray(rays_o, rays_d, r);
-  float t1 = __ldg(hits_t + 2 * r);
-  const float t2 = __ldg(hits_t + 2 * r + 1);
-  if (t1 >= 0) t1 = __fmaf_rn(calc_dt(t1, p), __ldg(noise + r), t1);
-  float t = t1; int k = 0; Probe s;
-  while (t < t2 && k < n_samples) {
-    if (march_probe(ray, p, t, s)) {
-      const int64_t o = start + k;
-      if (o < cap) {
-        xyzs[3 * o] = s.x; xyzs[3 * o + 1] = s.y; xyzs[3 * o + 2] = s.z;
-        dirs[3 * o] = ray.dx; dirs[3 * o + 1] = ray.dy; dirs[3 * o + 2] = ray.dz;
-        ts[o] = t; deltas[o] = s.dt;
-      }
-      t = __fadd_rn(t, s.dt); k++;
-    }
+  const float* tsrc = t_scratch + r * (int64_t)p.max_samples;
+  for (int k = lane; k < n_samples; k += 32) {
+    const int64_t o = start + k;
+    if (o >= cap) break;
+    const float t = ld_stream_f32(tsrc + k);
+    xyzs[3 * o] = __fmaf_rn(ray.dx, t, ray.ox); xyzs[3 * o + 1] = __fmaf_rn(ray.dy, t, ray.oy); xyzs[3 * o + 2] = __fmaf_rn(ray.dz, t, ray.oz);
+    dirs[3 * o] = ray.dx; dirs[3 * o + 1] = ray.dy; dirs[3 * o + 2] = ray.dz;
+    ts[o] = t; deltas[o] = calc_dt(t, p);
   }
 }
 
 // ---- test time -------------------------------------------------------------------------------
-// One thread per alive ray; the (n_alive, N_samples) slabs are written completely (zeros
-// behind N_eff) so the caller never memsets (raymarching.cu:421-426 does).
-__global__ void __launch_bounds__(128) march_test_kernel(
+// Warp per alive ray; the (n_alive, N_samples) slabs are written completely (zeros behind N_eff)
+// so the caller never memsets (raymarching.cu:421-426 does).
+template <bool kConstDt>
+__global__ void __launch_bounds__(256) march_test_kernel(
     const float* __restrict__ rays_o, const float* __restrict__ rays_d, float* __restrict__ hits_t,
     const int64_t* __restrict__ alive, int64_t n_alive, MarchParams p, int N_samples,
     float* __restrict__ xyzs, float* __restrict__ dirs, float* __restrict__ deltas, float* __restrict__ ts,
     int32_t* __restrict__ n_eff) {
-  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t n = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (n >= n_alive) return;
   const int64_t r = alive[n];
   const Ray ray = load_ray(rays_o, rays_d, r);
-  float t = hits_t[2 * r];
+  const float t = hits_t[2 * r];
   const float t2 = hits_t[2 * r + 1];
-  int k = 0; Probe s;
-  float t_resume = t;
   const int64_t o0 = n * N_samples;
-  while (t < t2 && k < N_samples) {
-    if (march_probe(ray, p, t, s)) {
-      const int64_t o = o0 + k;
-      xyzs[3 * o] = s.x; xyzs[3 * o + 1] = s.y; xyzs[3 * o + 2] = s.z;
-      dirs[3 * o] = ray.dx; dirs[3 * o + 1] = ray.dy; dirs[3 * o + 2] = ray.dz;
-      ts[o] = t; deltas[o] = s.dt;
-      t = __fadd_rn(t, s.dt); k++;
-      t_resume = t;  // only a taken sample moves the resume point (raymarching.cu:389-391)
-    }
+  float t_next = t;
+  // unlike the training kernel the reference's test loop has no `0 <= t` guard (raymarching.cu:365)
+  int k = 0;
+  if (t < t2) k = march_ray_warp<kConstDt>(ray, p, p.bitfield, t, t2, N_samples, ts + o0, t_next);
+  __syncwarp();
+  if (lane == 0) {
+    if (k > 0) hits_t[2 * r] = t_next;   // only a taken sample moves the resume point (raymarching.cu:389-391)
+    n_eff[n] = k;
   }
-  if (k > 0) hits_t[2 * r] = t_resume;
-  n_eff[n] = k;
-  for (int j = k; j < N_samples; j++) {
+  for (int j = lane; j < N_samples; j += 32) {
     const int64_t o = o0 + j;
-    xyzs[3 * o] = 0.f; xyzs[3 * o + 1] = 0.f; xyzs[3 * o + 2] = 0.f;
-    dirs[3 * o] = 0.f; dirs[3 * o + 1] = 0.f; dirs[3 * o + 2] = 0.f;
-    ts[o] = 0.f; deltas[o] = 0.f;
+    if (j < k) {
+      const float tj = ts[o];
+      xyzs[3 * o] = __fmaf_rn(ray.dx, tj, ray.ox); xyzs[3 * o + 1] = __fmaf_rn(ray.dy, tj, ray.oy); xyzs[3 * o + 2] = __fmaf_rn(ray.dz, tj, ray.oz);
+      dirs[3 * o] = ray.dx; dirs[3 * o + 1] = ray.dy; dirs[3 * o + 2] = ray.dz;
+      deltas[o] = calc_dt(tj, p);
+    } else {
+      xyzs[3 * o] = 0.f; xyzs[3 * o + 1] = 0.f; xyzs[3 * o + 2] = 0.f;
+      dirs[3 * o] = 0.f; dirs[3 * o + 1] = 0.f; dirs[3 * o + 2] = 0.f;
+      ts[o] = 0.f; deltas[o] = 0.f;
+    }
   }
 }
 
@@ -139,29 +142,34 @@ extern "C" {
 int rnb_raymarching_train_count(const float* rays_o, const float* rays_d, const float* hits_t,
                                 const uint8_t* density_bitfield, int cascades, float scale,
                                 float exp_step_factor, const float* noise, int grid_size, int max_samples,
-                                int64_t n_rays, int64_t* rays_a, int32_t* counter, rnb_stream_t stream) {
+                                int64_t n_rays, int64_t* rays_a, int32_t* counter, float* t_scratch,
+                                rnb_stream_t stream) {
   const char* what = "rnb_raymarching_train_count";
   RNB_REQUIRE(n_rays >= 0 && cascades >= 1 && grid_size >= 1 && grid_size <= 1024 && max_samples >= 1, what);
   RNB_REQUIRE(counter != nullptr, what);
-  RNB_REQUIRE(n_rays == 0 || (rays_o && rays_d && hits_t && density_bitfield && noise && rays_a), what);
+  RNB_REQUIRE(n_rays == 0 || (rays_o && rays_d && hits_t && density_bitfield && noise && rays_a && t_scratch), what);
   const MarchParams p = make_march_params(density_bitfield, cascades, scale, exp_step_factor, grid_size, max_samples, scale);
-  if (n_rays > 0)
-    march_train_count_kernel<<<ceil_div(n_rays, 64), 64, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, noise, p, n_rays, rays_a);
+  if (n_rays > 0) {
+    const int grid = ceil_div(n_rays * 32, 256);
+    if (exp_step_factor == 0.0f)
+      march_train_count_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, noise, p, n_rays, rays_a, t_scratch);
+    else
+      march_train_count_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, noise, p, n_rays, rays_a, t_scratch);
+  }
   march_train_scan_kernel<<<1, 1024, 0, as_stream(stream)>>>(n_rays, rays_a, counter);
   return check_launch(what);
 }
 
-int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, const float* hits_t,
-                                const uint8_t* density_bitfield, int cascades, float scale,
-                                float exp_step_factor, const float* noise, int grid_size, int max_samples,
-                                int64_t n_rays, const int64_t* rays_a, int64_t cap, float* xyzs, float* dirs,
-                                float* deltas, float* ts, rnb_stream_t stream) {
+int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, float scale, float exp_step_factor,
+                                int grid_size, int max_samples, int64_t n_rays, const int64_t* rays_a,
+                                const float* t_scratch, int64_t cap, float* xyzs, float* dirs, float* deltas,
+                                float* ts, rnb_stream_t stream) {
   const char* what = "rnb_raymarching_train_write";
-  RNB_REQUIRE(n_rays >= 0 && cap >= 0 && cascades >= 1 && grid_size >= 1 && grid_size <= 1024 && max_samples >= 1, what);
+  RNB_REQUIRE(n_rays >= 0 && cap >= 0 && grid_size >= 1 && grid_size <= 1024 && max_samples >= 1, what);
   if (n_rays == 0 || cap == 0) return RNB_OK;
-  RNB_REQUIRE(rays_o && rays_d && hits_t && density_bitfield && noise && rays_a && xyzs && dirs && deltas && ts, what);
-  const MarchParams p = make_march_params(density_bitfield, cascades, scale, exp_step_factor, grid_size, max_samples, scale);
-  march_train_write_kernel<<<ceil_div(n_rays, 64), 64, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, noise, p, n_rays, rays_a, cap, xyzs, dirs, deltas, ts);
+  RNB_REQUIRE(rays_o && rays_d && rays_a && t_scratch && xyzs && dirs && deltas && ts, what);
+  const MarchParams p = make_march_params(nullptr, 1, scale, exp_step_factor, grid_size, max_samples, scale);
+  march_train_write_kernel<<<ceil_div(n_rays * 32, 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, p, n_rays, rays_a, t_scratch, cap, xyzs, dirs, deltas, ts);
   return check_launch(what);
 }
 
@@ -175,7 +183,11 @@ int rnb_raymarching_test(const float* rays_o, const float* rays_d, float* hits_t
   RNB_REQUIRE(rays_o && rays_d && hits_t && alive_indices && density_bitfield && xyzs && dirs && deltas && ts && N_eff_samples, what);
   // hazard Q1: the reference's test kernel hands `cascades` to calc_dt where `scale` is expected
   const MarchParams p = make_march_params(density_bitfield, cascades, scale, exp_step_factor, grid_size, max_samples, (float)cascades);
-  march_test_kernel<<<ceil_div(n_alive, 128), 128, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, alive_indices, n_alive, p, N_samples, xyzs, dirs, deltas, ts, N_eff_samples);
+  const int grid = ceil_div(n_alive * 32, 256);
+  if (exp_step_factor == 0.0f)
+    march_test_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, alive_indices, n_alive, p, N_samples, xyzs, dirs, deltas, ts, N_eff_samples);
+  else
+    march_test_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(rays_o, rays_d, hits_t, alive_indices, n_alive, p, N_samples, xyzs, dirs, deltas, ts, N_eff_samples);
   return check_launch(what);
 }
 

@@ -1,0 +1,134 @@
+// march_warp.cuh -- warp-per-ray occupancy-grid marcher (B200-first redesign of
+// models/csrc/raymarching.cu:184-235 / :353-401 of the reference).
+//
+// The reference walks each ray in one thread: every loop iteration probes ONE grid cell with a
+// dependent byte load and then either takes a sample (t += dt) or skips to the voxel's exit face
+// (do t += dt while t < t_target).  Both branches advance t along the SAME chain
+//     c_0 = t_start,  c_{k+1} = c_k + calc_dt(c_k)           (fp32, round-to-nearest)
+// so the set of parameters a ray can ever visit does not depend on the occupancy; occupancy only
+// decides which chain elements are visited.  Here a warp owns a ray and processes the chain in
+// chunks of 32: lane j holds c_j, all 32 cells are probed in parallel (32 independent loads in
+// flight instead of one), every empty lane finds the first chain element at or behind its own
+// t_target by a 5-step binary search over the warp (SHFL), and the reference's visit order is
+// then replayed by a warp-uniform walk that hops over runs of occupied lanes with one FFS.
+// Visited+occupied lanes are the samples; their t is stored lane-contiguously.  The result is
+// bit-identical to the serial loop (same chain values, same comparisons).
+#pragma once
+#include "march.cuh"
+
+namespace rnb {
+
+struct CellProbe {
+  float x, y, z, dt;
+  bool occ;
+  float t_target;   // only meaningful when !occ
+};
+
+// Same arithmetic as march_probe() (march.cuh), without the data-dependent advance.
+__device__ __forceinline__ CellProbe probe_cell(const Ray& r, const MarchParams& p, const uint8_t* __restrict__ bitfield,
+                                                float tt, float dt) {
+  CellProbe s;
+  s.x = __fmaf_rn(r.dx, tt, r.ox); s.y = __fmaf_rn(r.dy, tt, r.oy); s.z = __fmaf_rn(r.dz, tt, r.oz);
+  s.dt = dt;
+  const float mx = fmaxf(fabsf(s.x), fmaxf(fabsf(s.y), fabsf(s.z)));
+  const int mp = min(p.cascades - 1, max(0, frexp_exponent(mx) + 1));
+  const int md = min(p.cascades - 1, max(0, frexp_exponent(fabsf(__fmul_rn(s.dt, p.gs_f)))));
+  const int mip = max(mp, md);
+  const float mip_bound = fminf(__uint_as_float((uint32_t)(mip - 1 + 127) << 23), p.scale);
+  const float mip_bound_inv = __fdiv_rn(1.0f, mip_bound);
+  const int nx = (int)fmaxf(0.0f, fminf(__fmul_rn(__fmul_rn(0.5f, __fmaf_rn(s.x, mip_bound_inv, 1.0f)), p.gs_f), p.gs_m1));
+  const int ny = (int)fmaxf(0.0f, fminf(__fmul_rn(__fmul_rn(0.5f, __fmaf_rn(s.y, mip_bound_inv, 1.0f)), p.gs_f), p.gs_m1));
+  const int nz = (int)fmaxf(0.0f, fminf(__fmul_rn(__fmul_rn(0.5f, __fmaf_rn(s.z, mip_bound_inv, 1.0f)), p.gs_f), p.gs_m1));
+  const uint32_t idx = (uint32_t)mip * p.grid_size3 + (spread3(nx) | (spread3(ny) << 1) | (spread3(nz) << 2));
+  const uint32_t byte = __ldg(bitfield + (idx >> 3));
+  s.occ = (byte >> (idx & 7)) & 1u;
+  const float tx = __fmul_rn(__fmaf_rn(mip_bound, __fmaf_rn(__fmul_rn(__fadd_rn(__fadd_rn((float)nx, 0.5f), r.hx), p.gs_inv), 2.0f, -1.0f), -s.x), r.ix);
+  const float ty = __fmul_rn(__fmaf_rn(mip_bound, __fmaf_rn(__fmul_rn(__fadd_rn(__fadd_rn((float)ny, 0.5f), r.hy), p.gs_inv), 2.0f, -1.0f), -s.y), r.iy);
+  const float tz = __fmul_rn(__fmaf_rn(mip_bound, __fmaf_rn(__fmul_rn(__fadd_rn(__fadd_rn((float)nz, 0.5f), r.hz), p.gs_inv), 2.0f, -1.0f), -s.z), r.iz);
+  s.t_target = __fadd_rn(tt, fmaxf(0.0f, fminf(tx, fminf(ty, tz))));
+  return s;
+}
+
+// Marches one ray with the whole warp.  All arguments are warp-uniform.
+//   t_start : first chain element (already perturbed for training), t2 : exit parameter
+//   budget  : maximum number of samples to take (max_samples, or N_samples at test time)
+//   t_out   : receives the t of sample k at t_out[k] (k < return value); may be nullptr
+//   t_next  : (out) chain element following the last sample taken (the test-time resume point);
+//             untouched when no sample was taken
+// Returns the number of samples.
+template <bool kConstDt>
+__device__ __forceinline__ int march_ray_warp(const Ray& ray, const MarchParams& p, const uint8_t* __restrict__ bitfield,
+                                              float t_start, float t2, int budget, float* __restrict__ t_out,
+                                              float& t_next) {
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  float tc = t_start;
+  float pending = -INFINITY;   // chain elements < pending are hopped over (a skip that left the previous chunk)
+  int n = 0;
+  if (!(tc >= 0.0f) || budget <= 0) return 0;
+  while (true) {
+    // ---- chain: lane j <- c_j ------------------------------------------------------------
+    float mine = tc;
+#pragma unroll
+    for (int k = 1; k < 32; k++) {
+      const float d = kConstDt ? p.dt_min : calc_dt(mine, p);
+      if (k <= lane) mine = __fadd_rn(mine, d);
+    }
+    const float my_dt = kConstDt ? p.dt_min : calc_dt(mine, p);
+    const bool valid = mine < t2;
+    const unsigned validmask = __ballot_sync(kFullMask, valid);   // a prefix of the lanes (chain is increasing)
+    const int nvalid = __popc(validmask);
+    // ---- probe all 32 cells ---------------------------------------------------------------
+    CellProbe s;
+    s.occ = false; s.t_target = 0.f;
+    if (valid) s = probe_cell(ray, p, bitfield, mine, my_dt);
+    const unsigned occmask = __ballot_sync(kFullMask, valid && s.occ);
+    // ---- next visited lane of every empty lane: first k > lane with !(c_k < t_target) -------
+    int lo = lane + 1, hi = 32;
+    if (occmask != validmask) {   // at least one empty valid lane (warp-uniform)
+#pragma unroll
+      for (int it = 0; it < 5; it++) {
+        const int mid = (lo + hi) >> 1;
+        const float cm = __shfl_sync(kFullMask, mine, mid & 31);
+        if (lo < hi) {
+          if (!(cm < s.t_target)) hi = mid; else lo = mid + 1;
+        }
+      }
+    }
+    const int nxt = lo;   // in [lane+1, 32]; 32 = leaves the chunk
+    // ---- replay the visit order (warp-uniform) ----------------------------------------------
+    int pos = __popc(__ballot_sync(kFullMask, mine < pending));   // first lane not hopped over
+    if (pos < 32) pending = -INFINITY;
+    unsigned samplemask = 0u;
+    bool done = false;
+    while (pos < 32) {
+      if (pos >= nvalid) { done = true; break; }           // c_pos >= t2: the ray left the box
+      if ((occmask >> pos) & 1u) {
+        const unsigned inv = (~occmask) >> pos;              // first non-occupied lane at or after pos
+        const int e = inv ? pos + __ffs(inv) - 1 : 32;
+        const int take = min(e - pos, budget - n);
+        samplemask |= (take >= 32 ? 0xffffffffu : ((1u << take) - 1u)) << pos;
+        n += take;
+        if (n >= budget) { done = true; break; }
+        pos = e;
+      } else {
+        const int nx = __shfl_sync(kFullMask, nxt, pos);
+        if (nx >= 32) pending = __shfl_sync(kFullMask, s.t_target, pos);
+        pos = nx;
+      }
+    }
+    // ---- emit this chunk's samples -----------------------------------------------------------
+    if (samplemask) {
+      const int n0 = n - __popc(samplemask);
+      if (t_out != nullptr && ((samplemask >> lane) & 1u)) t_out[n0 + __popc(samplemask & lt_mask)] = mine;
+      const int last = 31 - __clz(samplemask);
+      t_next = __shfl_sync(kFullMask, __fadd_rn(mine, my_dt), last);
+    }
+    if (done || nvalid < 32) break;
+    const float c31 = __shfl_sync(kFullMask, mine, 31), d31 = __shfl_sync(kFullMask, my_dt, 31);
+    tc = __fadd_rn(c31, d31);
+  }
+  return n;
+}
+
+}  // namespace rnb

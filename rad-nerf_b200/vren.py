@@ -72,6 +72,18 @@ def packbits(density_grid, density_threshold, density_bitfield):
          stream_arg(density_grid.device))
 
 
+_scratch_cache = {}
+
+
+def _scratch(dev, numel):
+    """Per-device reusable fp32 scratch (the marcher's per-ray sample-t rows)."""
+    buf = _scratch_cache.get(dev)
+    if buf is None or buf.numel() < numel:
+        buf = torch.empty(max(numel, 1), dtype=torch.float32, device=dev)
+        _scratch_cache[dev] = buf
+    return buf
+
+
 def raymarching_train(rays_o, rays_d, hits_t, density_bitfield, cascades, scale, exp_step_factor,
                       noise, grid_size, max_samples):
     """binding.cpp:60-81.  -> [rays_a (N,3) i64, xyzs (T,3), dirs (T,3), deltas (T), ts (T),
@@ -84,16 +96,17 @@ def raymarching_train(rays_o, rays_d, hits_t, density_bitfield, cascades, scale,
     rays_a = torch.empty(n_rays, 3, dtype=torch.int64, device=dev)
     counter = torch.empty(2, dtype=torch.int32, device=dev)
     st = stream_arg(dev)
+    t_scratch = _scratch(dev, n_rays * max_samples)   # un-initialised; only sample slots are written
     call("rnb_raymarching_train_count", rays_o, rays_d, hits_t, density_bitfield, i32(cascades), f32(scale),
-         f32(exp_step_factor), noise, i32(grid_size), i32(max_samples), i64(n_rays), rays_a, counter, st)
+         f32(exp_step_factor), noise, i32(grid_size), i32(max_samples), i64(n_rays), rays_a, counter,
+         t_scratch, st)
     total = int(counter[0].item())  # the reference syncs here too (custom_functions.py:91-96)
     xyzs = torch.empty(total, 3, dtype=torch.float32, device=dev)
     dirs = torch.empty(total, 3, dtype=torch.float32, device=dev)
     deltas = torch.empty(total, dtype=torch.float32, device=dev)
     ts = torch.empty(total, dtype=torch.float32, device=dev)
-    call("rnb_raymarching_train_write", rays_o, rays_d, hits_t, density_bitfield, i32(cascades), f32(scale),
-         f32(exp_step_factor), noise, i32(grid_size), i32(max_samples), i64(n_rays), rays_a, i64(total),
-         xyzs, dirs, deltas, ts, st)
+    call("rnb_raymarching_train_write", rays_o, rays_d, f32(scale), f32(exp_step_factor), i32(grid_size),
+         i32(max_samples), i64(n_rays), rays_a, t_scratch, i64(total), xyzs, dirs, deltas, ts, st)
     return [rays_a, xyzs, dirs, deltas, ts, counter]
 
 
