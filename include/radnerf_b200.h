@@ -193,6 +193,62 @@ int rnb_mlp_bwd(const rnb_mlp_desc* desc, const void* weights_f16, const void* i
                 const void* hidden_f16, const void* out_f16, const void* dL_dout_f16, int64_t n,
                 void* dL_din_f16, float* grad_weights, float grad_scale, rnb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * (3+4 fused) the field of all K sub-NeRFs on one packed sample list: hash-grid encode ->
+ *     geo MLP -> TruncExp -> SH4 -> rgb MLP in ONE kernel per direction (forward / backward).
+ *     Replaces the chain MNGP.forward = xyz_encoder -> geo_net_i -> TruncExp -> dir_encoder ->
+ *     cat -> rgb_net_i (models/networks.py:291-328) and its autograd backward (tinycudann
+ *     kernel_grid_backward + FullyFusedMLP backward).  The 32-feature row, the hidden
+ *     activations and the SH row never leave the SM in the forward pass unless the caller asks
+ *     for them to be saved for the backward pass.
+ * ------------------------------------------------------------------------------------ */
+#define RNB_MAX_K 16
+
+typedef struct {
+  int32_t K;                           /* sub-NeRFs sharing the hash table (model_zoo_size)         */
+  rnb_grid_meta grid;
+  float xyz_min[3], xyz_max[3];        /* MNGP.xyz_min / xyz_max (networks.py:300)                   */
+  const void* table_f16;               /* (entries,2) f16                                            */
+  const void* geo_w_f16[RNB_MAX_K];    /* geo_net_i: [64x32 | 32x64] f16, tinycudann layout          */
+  const void* rgb_w_f16[RNB_MAX_K];    /* rgb_net_i: [64x32 | 64x64 | 16x64] f16                     */
+} rnb_field_params;
+
+/* Packed sample list of the K passes.  Pass i owns samples [seg[i], seg[i] + seg[K+1+i]); every
+ * seg[i] is a multiple of 128 (a 128-row tile never straddles two passes); seg[K] = end of the
+ * last pass rounded up to 128.  `seg` lives in DEVICE memory (written by the marcher's scan), so
+ * no host synchronisation is needed between marching and field evaluation. */
+typedef struct {
+  const float* rays_o;                 /* (n_rays,3) f32                                             */
+  const float* rays_d;                 /* (n_rays,3) f32, unnormalised (Q20)                         */
+  const int32_t* ray_id;               /* (capacity) i32: sample -> ray                              */
+  const float* ts;                     /* (capacity) f32: sample -> t   (x = o + t*d)                */
+  const int32_t* seg;                  /* device, (2K+1) i32, see above                              */
+  int64_t capacity;                    /* multiple of 128                                            */
+} rnb_samples;
+
+/* Activations saved by the forward pass for the backward pass (all (capacity, W) row-major f16).
+ * Any pointer may be NULL in inference (then nothing is saved). */
+typedef struct {
+  void* enc;      /* (cap,32) hash-grid features                                   */
+  void* rgb_in;   /* (cap,32) [SH4(16) | geometry feature(16)]                     */
+  void* geo_h;    /* (cap,64) geo hidden (post-ReLU)                               */
+  void* rgb_h1;   /* (cap,64)                                                      */
+  void* rgb_h2;   /* (cap,64)                                                      */
+  void* sraw;     /* (cap)    raw sigma output before TruncExp                     */
+} rnb_field_saved;
+
+/* out: sigmas (cap) f32 = exp(raw); rgb4 (cap,4) f16 = sigmoid(rgb_net)[:, :3] (+1 pad). */
+int rnb_field_fwd(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved,
+                  float* sigmas, void* rgb4_f16, rnb_stream_t stream);
+/* dL_dsigmas (cap) f32, dL_drgbs (cap,3) f32 (what composite_train_bw emits).  Gradients are
+ * ACCUMULATED (fp32) into grad_table (entries,2), grad_geo[i], grad_rgb[i] (tinycudann layouts).
+ * loss_scale: internal fp16 gradient scale (activations gradients are carried in fp16 like
+ * tinycudann; parameter gradients are un-scaled before accumulation). */
+int rnb_field_bwd(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved,
+                  const void* rgb4_f16, const float* dL_dsigmas, const float* dL_drgbs,
+                  float loss_scale, float* grad_table, float* const* grad_geo, float* const* grad_rgb,
+                  rnb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

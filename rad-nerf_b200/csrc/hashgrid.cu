@@ -17,48 +17,9 @@
 //    (red.global.add.v2.f32, one per corner for both features); on the dense coarse levels
 //    runs of lanes that hit the same entry are first combined with a segmented warp reduction
 //    so that one lane issues the reduction (warp-level atomics aggregation).
-#include "common.cuh"
+#include "hashgrid.cuh"
 
 namespace rnb {
-
-struct GridLevels {
-  int n_levels;
-  float scale[RNB_MAX_LEVELS];
-  uint32_t res[RNB_MAX_LEVELS];
-  uint32_t offset[RNB_MAX_LEVELS + 1];
-};
-
-__device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, uint32_t res, uint32_t size, bool dense) {
-  uint32_t idx;
-  if (dense) {
-    idx = x + y * res + z * res * res;
-    if (idx >= size) idx %= size;   // only the +1 corner on the upper boundary can leave the level
-  } else {
-    idx = x ^ (y * 2654435761u) ^ (z * 805459861u);
-    idx = ((size & (size - 1u)) == 0u) ? (idx & (size - 1u)) : (idx % size);
-  }
-  return idx;
-}
-
-// tcnn grid_index(): the dense index is accumulated while stride <= size; the level is hashed iff
-// the full dense grid does not fit (size < res^3).
-__device__ __forceinline__ bool level_is_dense(uint32_t res, uint32_t size) {
-  return (uint64_t)res * res * res <= (uint64_t)size;
-}
-
-struct Corner {
-  uint32_t cx, cy, cz;
-  float wx, wy, wz;
-};
-
-__device__ __forceinline__ Corner locate(float x, float y, float z, float scale) {
-  Corner c;
-  const float px = fmaf(scale, x, 0.5f), py = fmaf(scale, y, 0.5f), pz = fmaf(scale, z, 0.5f);
-  const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
-  c.cx = (uint32_t)(int)fx; c.cy = (uint32_t)(int)fy; c.cz = (uint32_t)(int)fz;
-  c.wx = px - fx; c.wy = py - fy; c.wz = pz - fz;
-  return c;
-}
 
 __global__ void __launch_bounds__(128) hashgrid_fwd_kernel(const float* __restrict__ xs, int64_t n,
                                                            const __half2* __restrict__ table, GridLevels g,
@@ -104,28 +65,6 @@ __global__ void __launch_bounds__(128) hashgrid_fwd_kernel(const float* __restri
   }
 }
 
-__device__ __forceinline__ void red_add_f32x2(float* addr, float a, float b) {
-  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
-}
-
-// Warp-aggregated scatter.  Consecutive lanes are consecutive samples of one ray, so lanes
-// that hit the same coarse entry form RUNS: a segmented warp reduction over runs of equal index
-// (5 shuffle steps) leaves the run total in the run's first lane, which issues one reduction.
-__device__ __forceinline__ void scatter_aggregated(float* grad_level, uint32_t idx, float g0, float g1, bool active) {
-  const int lane = threadIdx.x & 31;
-  const uint32_t key = active ? idx : 0xffffffffu;
-  const uint32_t prev = __shfl_up_sync(kFullMask, key, 1);
-  const unsigned heads = __ballot_sync(kFullMask, lane == 0 || prev != key);
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const float v0 = __shfl_down_sync(kFullMask, g0, o), v1 = __shfl_down_sync(kFullMask, g1, o);
-    // lane+o belongs to my run iff no run head lies in (lane, lane+o]
-    const unsigned between = ((heads >> lane) >> 1) & ((1u << o) - 1u);
-    if (lane + o < 32 && between == 0u) { g0 += v0; g1 += v1; }
-  }
-  if (active && ((heads >> lane) & 1u)) red_add_f32x2(grad_level + 2 * (size_t)idx, g0, g1);
-}
-
 __global__ void __launch_bounds__(128) hashgrid_bwd_kernel(const float* __restrict__ xs, int64_t n,
                                                            const __half2* __restrict__ dy, GridLevels g,
                                                            float grad_scale, float* __restrict__ grad,
@@ -163,24 +102,8 @@ __global__ void __launch_bounds__(256) sh4_fwd_kernel(const float* __restrict__ 
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float x = u[3 * i] * 2.f - 1.f, y = u[3 * i + 1] * 2.f - 1.f, z = u[3 * i + 2] * 2.f - 1.f;
-  const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
   float o[16];
-  o[0] = 0.28209479177387814f;
-  o[1] = -0.48860251190291987f * y;
-  o[2] = 0.48860251190291987f * z;
-  o[3] = -0.48860251190291987f * x;
-  o[4] = 1.0925484305920792f * xy;
-  o[5] = -1.0925484305920792f * yz;
-  o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
-  o[7] = -1.0925484305920792f * xz;
-  o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
-  o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
-  o[10] = 2.8906114426405538f * xy * z;
-  o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
-  o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
-  o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
-  o[14] = 1.4453057213202769f * z * (x2 - y2);
-  o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+  sh4_eval(x, y, z, o);
   uint32_t p[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) { const __half2 h = __floats2half2_rn(o[2 * k], o[2 * k + 1]); p[k] = *reinterpret_cast<const uint32_t*>(&h); }
@@ -198,18 +121,6 @@ __global__ void __launch_bounds__(256) cast_f32_f16_kernel(const float* __restri
     reinterpret_cast<uint2*>(dst)[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
   }
   for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = __float2half_rn(src[i]);
-}
-
-static int to_levels(const rnb_grid_meta* m, GridLevels* g, const char* what) {
-  RNB_REQUIRE(m != nullptr, what);
-  RNB_REQUIRE(m->n_levels >= 1 && m->n_levels <= RNB_MAX_LEVELS && m->n_features == 2, what);
-  g->n_levels = m->n_levels;
-  for (int l = 0; l < m->n_levels; l++) {
-    g->scale[l] = m->scale[l]; g->res[l] = m->res[l]; g->offset[l] = m->offset[l];
-    RNB_REQUIRE(m->offset[l + 1] > m->offset[l] && m->res[l] >= 2, what);
-  }
-  g->offset[m->n_levels] = m->offset[m->n_levels];
-  return RNB_OK;
 }
 
 }  // namespace rnb
