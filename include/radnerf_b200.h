@@ -249,6 +249,76 @@ int rnb_field_bwd(const rnb_field_params* P, const rnb_samples* S, const rnb_fie
                   float loss_scale, float* grad_table, float* const* grad_geo, float* const* grad_rgb,
                   rnb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * (fused step) One Rad-NeRF training step without host synchronisation.  Replaces the body of
+ *     NeRFSystem.training_step (train_ml.py:172-200) below the data loader: Ray_Gate forward
+ *     (networks.py:1087-1093), ml_render's K-loop (ml_rendering.py:47-68: AABB, RayMarcher, MNGP.forward,
+ *     VolumeRenderer, background blend, gated blend), NeRFLoss (losses.py:52-74), the backward of all
+ *     of it, and the Adam update -- about 12 kernel launches, sample counts stay on the device.
+ *     The library allocates nothing: rnb_engine_layout() tells the caller how to carve ONE workspace
+ *     buffer (offsets in bytes), so the host side can also view every intermediate as a tensor.
+ * ------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t K;                     /* model_zoo_size; K == 1: single NGP field, no gate                       */
+  int32_t n_rays;                /* rays per step on this rank                                               */
+  int32_t max_samples;           /* MAX_SAMPLES = 1024 (ml_rendering.py:8)                                   */
+  int32_t grid_size;             /* 128                                                                      */
+  int32_t cascades;
+  float scale;
+  float exp_step_factor;
+  float T_threshold;             /* 1e-4                                                                     */
+  float near_distance;           /* NEAR_DISTANCE = 0.01 (ml_rendering.py:9)                                 */
+  int64_t sample_capacity;       /* samples of all K passes the workspace holds (multiple of 128)            */
+  rnb_grid_meta grid;
+  float xyz_min[3], xyz_max[3], center[3], half_size[3];
+  float lambda_opacity, lambda_cv, lambda_dm;
+  float loss_scale;              /* fp16 gradient scale inside the MLP chains (e.g. 128*1024)                */
+  /* flat parameter vector layout (element offsets): [hash table | geo_i, rgb_i ... | gate] */
+  int64_t n_params;
+  int64_t table_off;
+  int64_t geo_off[RNB_MAX_K];
+  int64_t rgb_off[RNB_MAX_K];
+  int64_t gate_off;              /* ignored when K == 1                                                      */
+} rnb_engine_config;
+
+/* byte offsets into the caller's workspace (all 256-byte aligned) */
+typedef struct {
+  int64_t total_bytes;
+  int64_t gate_in, gate_hidden, gate_logits, gate_dlogits, gate_prob, dgate;  /* f16 (R,16) | f16 (4,R,64) | f16 (R,16) | f16 (R,16) | f32 (R,K) | f32 (R,K) */
+  int64_t importance;            /* f32 (K): sum over rays of the gate (Ray_Gate's importance)                */
+  int64_t t_scratch;             /* f32 (K,R,max_samples)                                                     */
+  int64_t counts, starts;        /* i32 (K,R): samples per ray / first sample (index into the packed list)    */
+  int64_t seg;                   /* i32 (2K+1) pass bases + counts (rnb_samples.seg), then [2K+1] = overflow flag, [2K+2] = total samples */
+  int64_t ray_id, ts, deltas;    /* i32 | f32 | f32 (S)                                                       */
+  int64_t enc, rgb_in, geo_h, rgb_h1, rgb_h2, sraw;   /* rnb_field_saved                                     */
+  int64_t sigmas, rgb4, ws, dsigmas, drgbs;            /* f32 (S) | f16 (S,4) | f32 (S) | f32 (S) | f32 (S,3) */
+  int64_t pass_opacity, pass_depth, pass_rgb, pass_total;  /* f32 (K,R) | f32 (K,R) | f32 (K,R,3) (before background) | i32 (K,R) */
+  int64_t d_pass_opacity, d_pass_depth, d_pass_rgb;        /* gradient seeds, same shapes                     */
+  int64_t rgb, opacity, depth;   /* results: f32 (R,3) | f32 (R) | f32 (R,K)  (ml_rendering.py:72-77)         */
+  int64_t loss;                  /* f32 (8): [total, rgb, opacity, cv_importance, depth_mutual, -, -, -]      */
+} rnb_engine_layout;
+
+int rnb_engine_layout_of(const rnb_engine_config* cfg, rnb_engine_layout* out);
+
+/* Phase 1 (K > 1): gate forward.  Writes gate_prob and the LOCAL importance sums. params_f16: flat fp16
+ * copy of the parameter vector. */
+int rnb_engine_gate(const rnb_engine_config* cfg, void* workspace, const void* params_f16,
+                    const float* rays_o, const float* rays_d, rnb_stream_t stream);
+/* Phase 2: march, field, composite, blend, loss, and the complete backward.  `importance` (K) f32 device:
+ * the GLOBAL importance (all-reduced over ranks when data parallel; the workspace's own buffer otherwise).
+ * n_rays_global: rays of the whole (multi-rank) batch, the denominator of the loss means.
+ * bitfields: HOST array of K device pointers; noise (K,n_rays) f32 device in [0,1); bg (K,3) f32 HOST
+ * (background colour per pass, Q17).  Gradients are ACCUMULATED into grads_f32 (flat, fp32). */
+int rnb_engine_fwd_bwd(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* grads_f32,
+                       const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
+                       const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
+                       const float* importance, int with_backward, rnb_stream_t stream);
+/* Phase 3: Adam (torch.optim.Adam semantics, no weight decay) over the flat vector; writes the fp16 copy
+ * and ZEROES the gradient for the next step.  grad_scale multiplies the gradient first. */
+int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq,
+                    int64_t n, float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
+                    rnb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

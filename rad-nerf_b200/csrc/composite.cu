@@ -8,24 +8,9 @@
 // termination index (total_samples) are bit-identical to the reference's one-thread-per-ray
 // loop (volumerendering.cu:27-44), while the per-ray sums are warp tree reductions (fp32
 // re-association only).  HBM-bound: 28 B/sample forward, 48 B/sample backward.
-#include "common.cuh"
+#include "composite.cuh"
 
 namespace rnb {
-
-// Serial transmittance over the 32 lanes.  On entry T_in = transmittance before lane 0's
-// sample (warp-uniform); returns this lane's transmittance BEFORE its sample and updates
-// T_in to the value after lane 31's sample.
-__device__ __forceinline__ float serial_T(float one_minus_a, float& T_in, int lane) {
-  float run = T_in, mine = T_in;
-#pragma unroll
-  for (int j = 0; j < 32; j++) {
-    const float om = __shfl_sync(kFullMask, one_minus_a, j);
-    if (lane == j) mine = run;
-    run = __fmul_rn(run, om);
-  }
-  T_in = run;
-  return mine;
-}
 
 __global__ void __launch_bounds__(256) composite_train_fw_kernel(
     const float* __restrict__ sigmas, const float* __restrict__ rgbs, const float* __restrict__ deltas,
@@ -37,43 +22,13 @@ __global__ void __launch_bounds__(256) composite_train_fw_kernel(
   if (n >= n_rays) return;
   const int64_t ray_idx = rays_a[3 * n], start = rays_a[3 * n + 1];
   const int N = (int)rays_a[3 * n + 2];
-  float T = 1.0f, R = 0.f, G = 0.f, B = 0.f, D = 0.f, O = 0.f;
-  int total = N;
-  int base = 0;
-  for (; base < N; base += 32) {
-    const int k = base + lane;
-    const bool valid = k < N;
-    const int64_t s = start + k;
-    float a = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, tt = 0.f;
-    if (valid) {
-      a = 1.0f - __expf(-ld_stream_f32(sigmas + s) * ld_stream_f32(deltas + s));
-      cr = ld_stream_f32(rgbs + 3 * s); cg = ld_stream_f32(rgbs + 3 * s + 1); cb = ld_stream_f32(rgbs + 3 * s + 2);
-      tt = ld_stream_f32(ts + s);
-    }
-    const float om = 1.0f - a;
-    const float Tb = serial_T(om, T, lane);
-    const float Ta = __fmul_rn(Tb, om);
-    const unsigned term = __ballot_sync(kFullMask, valid && Ta <= T_threshold);
-    const int first = term ? (__ffs(term) - 1) : 32;
-    const float w = (valid && lane <= first) ? __fmul_rn(a, Tb) : 0.f;
-    if (valid) ws[s] = w;
-    R = fmaf(w, cr, R); G = fmaf(w, cg, G); B = fmaf(w, cb, B); D = fmaf(w, tt, D); O += w;
-    if (term) { total = base + first; base += 32; break; }
-  }
-  // samples behind the terminating chunk keep ws = 0 (reference: zero-initialised, Q8)
-  for (int k = base + lane; k < N; k += 32) ws[start + k] = 0.f;
-  R = warp_sum(R); G = warp_sum(G); B = warp_sum(B); D = warp_sum(D); O = warp_sum(O);
+  const RayAccum r = composite_fw_segment<false>(sigmas, rgbs, deltas, ts, start, N, T_threshold, ws);
   if (lane == 0) {
-    rgb[3 * ray_idx] = R; rgb[3 * ray_idx + 1] = G; rgb[3 * ray_idx + 2] = B;
-    depth[ray_idx] = D; opacity[ray_idx] = O; total_samples[ray_idx] = total;
+    rgb[3 * ray_idx] = r.R; rgb[3 * ray_idx + 1] = r.G; rgb[3 * ray_idx + 2] = r.B;
+    depth[ray_idx] = r.D; opacity[ray_idx] = r.O; total_samples[ray_idx] = r.total;
   }
 }
 
-// Backward (volumerendering.cu:109-151).  Per sample, with T = transmittance AFTER the sample
-// and r,g,b,d the inclusive prefix sums of w*c / w*t:
-//   dL_drgbs = dL_drgb * w
-//   dL_dsigma = delta * ( sum_c dL_drgb_c * (c*T - (C - c_prefix)) + dL_dopacity * (1 - O)
-//                         + dL_ddepth * (t*T - (D - d)) + T*dL_dws - (sum(dL_dws*ws) - prefix) )
 __global__ void __launch_bounds__(256) composite_train_bw_kernel(
     const float* __restrict__ dL_dopacity, const float* __restrict__ dL_ddepth, const float* __restrict__ dL_drgb,
     const float* __restrict__ dL_dws, const float* __restrict__ sigmas, const float* __restrict__ rgbs,
@@ -81,63 +36,17 @@ __global__ void __launch_bounds__(256) composite_train_bw_kernel(
     const int64_t* __restrict__ rays_a, const float* __restrict__ opacity, const float* __restrict__ depth,
     const float* __restrict__ rgb, float T_threshold, int64_t n_rays, float* __restrict__ dL_dsigmas,
     float* __restrict__ dL_drgbs) {
-  const int lane = threadIdx.x & 31;
   const int64_t n = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (n >= n_rays) return;
   const int64_t ray_idx = rays_a[3 * n], start = rays_a[3 * n + 1];
   const int N = (int)rays_a[3 * n + 2];
   if (N == 0) return;
-  const float Rf = rgb[3 * ray_idx], Gf = rgb[3 * ray_idx + 1], Bf = rgb[3 * ray_idx + 2];
-  const float Of = opacity[ray_idx], Df = depth[ray_idx];
-  const float gr = dL_drgb[3 * ray_idx], gg = dL_drgb[3 * ray_idx + 1], gb = dL_drgb[3 * ray_idx + 2];
-  const float gO = dL_dopacity[ray_idx], gD = dL_ddepth[ray_idx];
-  float ws_total = 0.f;
-  if (dL_dws) {
-    for (int k = lane; k < N; k += 32) ws_total = fmaf(dL_dws[start + k], ws[start + k], ws_total);
-    ws_total = warp_sum(ws_total);
-  }
-  float T = 1.0f, r = 0.f, g = 0.f, b = 0.f, d = 0.f, wsrun = 0.f;  // carries (warp-uniform)
-  int base = 0;
-  for (; base < N; base += 32) {
-    const int k = base + lane;
-    const bool valid = k < N;
-    const int64_t s = start + k;
-    float a = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, tt = 0.f, dl = 0.f, gw = 0.f, wv = 0.f;
-    if (valid) {
-      dl = ld_stream_f32(deltas + s);
-      a = 1.0f - __expf(-ld_stream_f32(sigmas + s) * dl);
-      cr = ld_stream_f32(rgbs + 3 * s); cg = ld_stream_f32(rgbs + 3 * s + 1); cb = ld_stream_f32(rgbs + 3 * s + 2);
-      tt = ld_stream_f32(ts + s);
-      if (dL_dws) { gw = ld_stream_f32(dL_dws + s); wv = ld_stream_f32(ws + s); }
-    }
-    const float om = 1.0f - a;
-    const float Tb = serial_T(om, T, lane);
-    const float Ta = __fmul_rn(Tb, om);
-    const unsigned term = __ballot_sync(kFullMask, valid && Ta <= T_threshold);
-    const int first = term ? (__ffs(term) - 1) : 32;
-    const bool live = valid && lane <= first;
-    const float w = live ? __fmul_rn(a, Tb) : 0.f;
-    const float pr = r + warp_incl_scan(w * cr, lane), pg = g + warp_incl_scan(w * cg, lane);
-    const float pb = b + warp_incl_scan(w * cb, lane), pd = d + warp_incl_scan(w * tt, lane);
-    const float pw = wsrun + warp_incl_scan(live ? gw * wv : 0.f, lane);
-    if (valid) {
-      float gs = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f;
-      if (live) {
-        g0 = gr * w; g1 = gg * w; g2 = gb * w;
-        gs = dl * (gr * (cr * Ta - (Rf - pr)) + gg * (cg * Ta - (Gf - pg)) + gb * (cb * Ta - (Bf - pb)) +
-                   gO * (1.0f - Of) + gD * (tt * Ta - (Df - pd)) + Ta * gw - (ws_total - pw));
-      }
-      dL_dsigmas[s] = gs;
-      dL_drgbs[3 * s] = g0; dL_drgbs[3 * s + 1] = g1; dL_drgbs[3 * s + 2] = g2;
-    }
-    if (term) { base += 32; break; }
-    r = __shfl_sync(kFullMask, pr, 31); g = __shfl_sync(kFullMask, pg, 31); b = __shfl_sync(kFullMask, pb, 31);
-    d = __shfl_sync(kFullMask, pd, 31); wsrun = __shfl_sync(kFullMask, pw, 31);
-  }
-  for (int k = base + lane; k < N; k += 32) {
-    const int64_t s = start + k;
-    dL_dsigmas[s] = 0.f; dL_drgbs[3 * s] = 0.f; dL_drgbs[3 * s + 1] = 0.f; dL_drgbs[3 * s + 2] = 0.f;
-  }
+  RayGrad q;
+  q.Rf = rgb[3 * ray_idx]; q.Gf = rgb[3 * ray_idx + 1]; q.Bf = rgb[3 * ray_idx + 2];
+  q.Of = opacity[ray_idx]; q.Df = depth[ray_idx];
+  q.gr = dL_drgb[3 * ray_idx]; q.gg = dL_drgb[3 * ray_idx + 1]; q.gb = dL_drgb[3 * ray_idx + 2];
+  q.gO = dL_dopacity[ray_idx]; q.gD = dL_ddepth[ray_idx];
+  composite_bw_segment<false>(q, dL_dws, sigmas, rgbs, ws, deltas, ts, start, N, T_threshold, dL_dsigmas, dL_drgbs);
 }
 
 // Test-time in-place compositing (volumerendering.cu:206-250): one thread per alive ray

@@ -2,7 +2,7 @@
 // Replaces models/csrc/intersection.cu and raymarching.cu:35-161 of the reference.
 #include <stdarg.h>
 
-#include "common.cuh"
+#include "aabb.cuh"
 
 namespace rnb {
 
@@ -20,18 +20,6 @@ void set_error(const char* fmt, ...) {
 // max_hits rows are ordered by ascending t1 like the reference's torch::sort (:95-97), which
 // places unfilled (-1) rows first.  For the path's only configuration (1 voxel, 1 hit)
 // this is a single slab test and three coalesced stores.
-__device__ __forceinline__ float2 slab_test(float ox, float oy, float oz, float ix, float iy, float iz,
-                                            float cx, float cy, float cz, float hx, float hy, float hz) {
-  // same operation order as intersection.cu:12-21: (center -/+ half_size - ray_o) * inv_d
-  const float ax = __fmul_rn(__fsub_rn(__fsub_rn(cx, hx), ox), ix), bx = __fmul_rn(__fsub_rn(__fadd_rn(cx, hx), ox), ix);
-  const float ay = __fmul_rn(__fsub_rn(__fsub_rn(cy, hy), oy), iy), by = __fmul_rn(__fsub_rn(__fadd_rn(cy, hy), oy), iy);
-  const float az = __fmul_rn(__fsub_rn(__fsub_rn(cz, hz), oz), iz), bz = __fmul_rn(__fsub_rn(__fadd_rn(cz, hz), oz), iz);
-  const float t1 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
-  const float t2 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
-  if (t1 > t2) return make_float2(-1.0f, -1.0f);
-  return make_float2(t1, t2);
-}
-
 template <bool kSphere>
 __global__ void __launch_bounds__(256) ray_prim_intersect_kernel(
     const float* __restrict__ rays_o, const float* __restrict__ rays_d,

@@ -1,0 +1,200 @@
+"""Fused Rad-NeRF training step (host side of rnb_engine_*, include/radnerf_b200.h).
+
+`Engine` takes the drop-in modules (`MNGP`/`NGP` + `Ray_Gate`, same classes the reference builds in
+train_ml.py:74-80), re-homes their flat tinycudann-layout parameters into ONE flat fp32 vector (the
+modules keep working: their `.params` become views), and runs the step of train_ml.py:172-200 --
+gate, K x (AABB, march, field, composite, background), gated blend, NeRFLoss, backward, Adam -- as
+~12 kernel launches without a host synchronisation.  Data parallel: rays shard by rank; the only
+exchanges are the K-float gate importance (before the non-linear CV loss) and one all-reduce of the
+flat gradient vector (NCCL over NVLink), both issued from here through torch.distributed.
+There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import call, f32, i32, i64, stream_arg
+from .field import MAX_K
+from .tcnn import _GridMeta
+
+
+class _Config(ctypes.Structure):
+    _fields_ = [("K", ctypes.c_int32), ("n_rays", ctypes.c_int32), ("max_samples", ctypes.c_int32),
+                ("grid_size", ctypes.c_int32), ("cascades", ctypes.c_int32), ("scale", ctypes.c_float),
+                ("exp_step_factor", ctypes.c_float), ("T_threshold", ctypes.c_float), ("near_distance", ctypes.c_float),
+                ("sample_capacity", ctypes.c_int64), ("grid", _GridMeta),
+                ("xyz_min", ctypes.c_float * 3), ("xyz_max", ctypes.c_float * 3), ("center", ctypes.c_float * 3),
+                ("half_size", ctypes.c_float * 3),
+                ("lambda_opacity", ctypes.c_float), ("lambda_cv", ctypes.c_float), ("lambda_dm", ctypes.c_float),
+                ("loss_scale", ctypes.c_float),
+                ("n_params", ctypes.c_int64), ("table_off", ctypes.c_int64),
+                ("geo_off", ctypes.c_int64 * MAX_K), ("rgb_off", ctypes.c_int64 * MAX_K), ("gate_off", ctypes.c_int64)]
+
+
+_LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_hidden", "gate_logits", "gate_dlogits", "gate_prob", "dgate", "importance",
+                  "t_scratch", "counts", "starts", "seg", "ray_id", "ts", "deltas", "enc", "rgb_in", "geo_h", "rgb_h1", "rgb_h2",
+                  "sraw", "sigmas", "rgb4", "ws", "dsigmas", "drgbs", "pass_opacity", "pass_depth", "pass_rgb", "pass_total",
+                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss"]
+
+
+class _Layout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int64) for n in _LAYOUT_FIELDS]
+
+
+class Engine:
+    def __init__(self, model, gate=None, n_rays=8192, exp_step_factor=0.0, samples_per_ray=128, max_samples=1024,
+                 T_threshold=1e-4, near_distance=0.01, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
+                 loss_scale=128.0 * 1024.0, lr=1e-2, betas=(0.9, 0.999), eps=1e-15):
+        _lib.lib()
+        self.model, self.gate = model, gate
+        self.K = K = getattr(model, "size", 1)
+        assert (gate is not None) == (K > 1), "a gate is needed iff model_zoo_size > 1"
+        dev = model.xyz_encoder.params.device
+        assert dev.type == "cuda", "the engine needs the model on a CUDA device (no CPU path)"
+        self.device, self.n_rays = dev, int(n_rays)
+        self.exp_step_factor = float(exp_step_factor)
+        # ---- flat parameter vector: [table | geo_i, rgb_i ... | gate] -------------------------------
+        mods = [("table", model.xyz_encoder)]
+        for i in range(K):
+            sfx = f"_{i}" if hasattr(model, "size") else ""
+            mods += [(f"geo{i}", getattr(model, "geo_net" + sfx)), (f"rgb{i}", getattr(model, "rgb_net" + sfx))]
+        if gate is not None:
+            mods.append(("gate", gate.encoder))
+        offs, off = {}, 0
+        for name, m in mods:
+            offs[name] = off
+            off += (m.params.numel() + 7) // 8 * 8      # keep every block 16-byte aligned in fp16
+        self.n_params = off
+        self.offsets = offs
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat16 = torch.zeros(off, dtype=torch.float16, device=dev)
+        self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
+        self._mods = mods
+        with torch.no_grad():
+            for name, m in mods:
+                n = m.params.numel()
+                self.flat[offs[name]:offs[name] + n].copy_(m.params.data)
+                m.params.data = self.flat[offs[name]:offs[name] + n]          # the module now views the flat vector
+                m._shadow.buf = self.flat16[offs[name]:offs[name] + n]        # ... and its fp16 copy
+                m._shadow.version = None
+        self.sync_params()
+        # ---- config / workspace -------------------------------------------------------------------------
+        c = _Config()
+        c.K, c.n_rays, c.max_samples, c.grid_size, c.cascades = K, self.n_rays, max_samples, model.grid_size, model.cascades
+        c.scale, c.exp_step_factor, c.T_threshold, c.near_distance = model.scale, exp_step_factor, T_threshold, near_distance
+        c.sample_capacity = (self.n_rays * K * int(samples_per_ray) + 127) // 128 * 128
+        ctypes.memmove(ctypes.byref(c.grid), ctypes.byref(model.xyz_encoder._meta), ctypes.sizeof(_GridMeta))
+        for name in ("xyz_min", "xyz_max", "center", "half_size"):
+            v = getattr(model, name).reshape(-1).tolist()
+            for k in range(3):
+                getattr(c, name)[k] = v[k]
+        c.lambda_opacity, c.lambda_cv, c.lambda_dm = lambda_opacity, (lambda_cv if K > 1 else 0.0), (lambda_dm if K > 1 else 0.0)
+        c.loss_scale = loss_scale
+        c.n_params, c.table_off = off, offs["table"]
+        for i in range(K):
+            c.geo_off[i], c.rgb_off[i] = offs[f"geo{i}"], offs[f"rgb{i}"]
+        c.gate_off = offs.get("gate", 0)
+        self.cfg = c
+        L = _Layout()
+        call("rnb_engine_layout_of", ctypes.byref(c), ctypes.byref(L))
+        self.layout = L
+        self.ws = torch.empty(L.total_bytes, dtype=torch.uint8, device=dev)
+        R, S = self.n_rays, c.sample_capacity
+        v = self._view
+        self.gate_prob = v("gate_prob", torch.float32, (R, K))
+        self.importance = v("importance", torch.float32, (MAX_K,))[:K]
+        self.seg = v("seg", torch.int32, (2 * MAX_K + 4,))
+        self.counts = v("counts", torch.int32, (K, R)); self.starts = v("starts", torch.int32, (K, R))
+        self.ts = v("ts", torch.float32, (S,)); self.deltas = v("deltas", torch.float32, (S,)); self.ray_id = v("ray_id", torch.int32, (S,))
+        self.sigmas = v("sigmas", torch.float32, (S,)); self.rgb4 = v("rgb4", torch.float16, (S, 4)); self.sample_ws = v("ws", torch.float32, (S,))
+        self.pass_rgb = v("pass_rgb", torch.float32, (K, R, 3)); self.pass_opacity = v("pass_opacity", torch.float32, (K, R))
+        self.pass_depth = v("pass_depth", torch.float32, (K, R)); self.pass_total = v("pass_total", torch.int32, (K, R))
+        self.rgb = v("rgb", torch.float32, (R, 3)); self.opacity = v("opacity", torch.float32, (R,)); self.depth = v("depth", torch.float32, (R, K))
+        self.loss = v("loss", torch.float32, (8,))
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.opt_step = 0
+        self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+    def _view(self, name, dtype, shape):
+        off = getattr(self.layout, name)
+        n = 1
+        for s in shape:
+            n *= s
+        nbytes = n * torch.empty(0, dtype=dtype).element_size()
+        return self.ws[off:off + nbytes].view(dtype).view(*shape)
+
+    # -- parameters -------------------------------------------------------------------------------------
+    def sync_params(self):
+        """Refresh the fp16 copies of modules whose fp32 parameters were changed through torch
+        (load_state_dict, manual edits); a no-op otherwise."""
+        for _, m in self._mods:
+            m._shadow.get(m.params)
+
+    def bitfields(self):
+        if self.K == 1 and not hasattr(self.model, "size"):
+            return [self.model.density_bitfield]
+        return [getattr(self.model, f"density_bitfield_{i}") for i in range(self.K)]
+
+    # -- phases -------------------------------------------------------------------------------------------
+    def forward_backward(self, rays_o, rays_d, target_rgb, noise, bg, with_backward=True):
+        """noise (K,R) f32 in [0,1); bg: K x 3 python floats.  Fills the result views and, with
+        `with_backward`, accumulates into self.grads.  Returns nothing; no host synchronisation."""
+        c = self.cfg
+        for t, n in ((rays_o, "rays_o"), (rays_d, "rays_d"), (target_rgb, "target_rgb"), (noise, "noise")):
+            _lib.check_input(t, n, torch.float32)
+        assert rays_o.shape[0] == self.n_rays and noise.numel() == self.K * self.n_rays
+        st = stream_arg(self.device)
+        if self.K > 1:
+            call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
+            if self.world > 1:      # CV loss is non-linear in the batch: the importance must be global
+                dist.all_reduce(self.importance)
+        bfs = self.bitfields()
+        bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
+        bg_arr = (ctypes.c_float * (3 * self.K))(*[float(x) for row in bg for x in row])
+        call("rnb_engine_fwd_bwd", ctypes.byref(c), self.ws, self.flat16, self.grads if with_backward else None,
+             rays_o, rays_d, target_rgb, noise, bf_arr, bg_arr, i64(self.n_rays * self.world),
+             self.importance if self.K > 1 else None, i32(1 if with_backward else 0), st)
+
+    def adam_step(self, lr=None):
+        if self.world > 1:
+            dist.all_reduce(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
+        self.opt_step += 1
+        call("rnb_engine_adam", self.flat, self.flat16, self.grads, self.exp_avg, self.exp_avg_sq, i64(self.n_params),
+             f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), i64(self.opt_step),
+             f32(1.0), stream_arg(self.device))
+
+    def background(self, random_bg=False):
+        if self.exp_step_factor == 0:
+            return [[1.0, 1.0, 1.0]] * self.K
+        if random_bg:
+            return torch.rand(self.K, 3).tolist()
+        return [[0.0, 0.0, 0.0]] * self.K
+
+    def step(self, rays_o, rays_d, target_rgb, lr=None, random_bg=False, noise=None):
+        """One training step.  Returns the loss vector view [total, rgb, opacity, cv, depth_mutual, ...] (device)."""
+        if noise is None:
+            noise = torch.rand(self.K, self.n_rays, device=self.device)
+        self.forward_backward(rays_o, rays_d, target_rgb, noise, self.background(random_bg), True)
+        self.adam_step(lr)
+        return self.loss
+
+    def results(self):
+        """The reference's ml_render result dict (ml_rendering.py:72-77) as views of the workspace."""
+        out = {"rgb": self.rgb, "depth": self.depth, "opacity": self.opacity,
+               "independent_rgbs": None, "pass_rgb": self.pass_rgb, "pass_opacity": self.pass_opacity}
+        if self.K > 1:
+            out["gating_code"] = self.gate_prob
+            out["gating_importance"] = self.importance
+        return out
+
+    def sample_stats(self):
+        """(samples per pass list, overflow flag) -- synchronises."""
+        seg = self.seg.tolist()
+        K = self.K
+        return seg[K + 1:2 * K + 1], bool(seg[2 * K + 1])
