@@ -100,19 +100,25 @@ def measured_peaks():
     return 6650.0, 1400.0, "fallback"
 
 
-# algorithmic HBM bytes of one launch of each entry point, as a function of the
-# samples N / rays R it processed
-ALGO_BYTES = {
-    "rnb_hashgrid_fwd": lambda N, R: 76 * N,
-    "rnb_hashgrid_bwd": lambda N, R: 76 * N,
-    "rnb_composite_train_fw": lambda N, R: 28 * N + 52 * R,
-    "rnb_composite_train_bw": lambda N, R: 48 * N + 64 * R,
-    "rnb_raymarching_train_write": lambda N, R: 32 * N + 60 * R,
-    "rnb_raymarching_train_count": lambda N, R: 60 * R,
+# Algorithmic work of one launch of each stage of the fused step (SURVEY.md 8d per-unit figures), as a
+# function of the samples N of all K passes and the K*R marched rays of that launch.
+#   bytes: march 60 B/ray + 32 B/sample (incl. expand); field fwd (fused) 34 B/sample; composite fw 28 B/sample
+#   + 52 B/ray; composite bw 48 B/sample + 64 B/ray; field bwd = encode bwd 76 B/sample; adam 28 B/param.
+#   flops: MLP fwd 18 944 FLOP/sample (unpadded), bwd 37 888 FLOP/sample; gate 25 344 + 128 K FLOP/ray.
+STAGES = ["gate", "march", "scan", "expand", "field_fwd", "composite_fw", "blend_loss", "composite_bw", "field_bwd",
+          "gate_bwd", "adam"]
+STAGE_BYTES = {
+    "march": lambda N, KR, P: 60 * KR + 20 * N,
+    "expand": lambda N, KR, P: 12 * N,
+    "field_fwd": lambda N, KR, P: 34 * N,
+    "composite_fw": lambda N, KR, P: 28 * N + 52 * KR,
+    "composite_bw": lambda N, KR, P: 48 * N + 64 * KR,
+    "field_bwd": lambda N, KR, P: 76 * N,
+    "adam": lambda N, KR, P: 28 * P,
 }
-ALGO_FLOPS = {  # MLP flops per row as executed (padded), fwd / bwd(dgrad+wgrad)
-    "rnb_mlp_fwd": 2 * (32 * 64 + 64 * 32),
-    "rnb_mlp_bwd": 4 * (32 * 64 + 64 * 32),
+STAGE_FLOPS = {
+    "field_fwd": lambda N, KR, P: 18944 * N,
+    "field_bwd": lambda N, KR, P: 37888 * N,
 }
 
 
@@ -168,6 +174,7 @@ def run_reference(args):
 
 
 def run_product(args):
+    import ctypes
     import torch
     import torch.distributed as dist
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -179,9 +186,10 @@ def run_product(args):
     syn, w = workload(args.workload)
     from radnerf_b200 import _lib
     from radnerf_b200.trainer import Trainer
-    _lib.lib()   # fail loudly if the CUDA library is missing: there is no fallback
+    lib = _lib.lib()   # fail loudly if the CUDA library is missing: there is no fallback
     K = w["K"]
-    tr = Trainer(scale=w["scale"], K=K, freeze_occupancy=True, device=f"cuda:{local}")
+    tr = Trainer(scale=w["scale"], K=K, freeze_occupancy=True, device=f"cuda:{local}", engine=not args.python_surface,
+                 batch_rays=BATCH)
     tr.set_occupancy(scene_bitfields(syn, w))
     host = [tuple(torch.from_numpy(a).pin_memory() for a in b) for b in make_batches(syn, w, rank)]
     dev = [tuple(a.cuda(non_blocking=True) for a in b) for b in host]
@@ -223,13 +231,20 @@ def run_product(args):
     flush_ms = timed(lambda s: flush.add_(1.0), args.steps) / args.steps
     clocks = ClockSampler(local); clocks.start()
     n0 = _lib.launch_count
-    _lib.profile_begin()
     ms = timed(dev_step, args.steps)
-    prof = _lib.profile_end()
     launches = _lib.launch_count - n0
     clk = clocks.stop()
     ms_step = ms / args.steps - flush_ms
     e2e_ms = timed(e2e_step, args.steps) / args.steps - flush_ms
+    # per-stage device time of the same steps (separate pass: CUDA events around every stage of the fused step)
+    stage_ms = {}
+    if tr.engine is not None:
+        lib.rnb_engine_profile(1)
+        timed(dev_step, args.steps)
+        arr_ms = (ctypes.c_double * 16)(); arr_n = (ctypes.c_int32 * 16)()
+        lib.rnb_engine_profile_read(arr_ms, arr_n, 16)
+        lib.rnb_engine_profile(0)
+        stage_ms = {STAGES[i]: (arr_ms[i] / max(arr_n[i], 1), arr_n[i]) for i in range(len(STAGES)) if arr_n[i]}
     rays_total = BATCH * world
     value = rays_total / (ms_step * 1e-3)
     e2e_val = rays_total / (e2e_ms * 1e-3)
@@ -237,49 +252,37 @@ def run_product(args):
         if world > 1:
             dist.destroy_process_group()
         return
-    # samples per sub-NeRF pass (for the algorithmic-bytes figures)
-    res = tr.last_results
     hbm, tflops, which = measured_peaks()
-    kern = sorted(((t, n, c) for n, (c, t) in prof.items()), reverse=True)
-    total_kernel_ms = sum(t for t, _, _ in kern)
-    # average samples per field pass, measured from the marcher's own counters
-    from radnerf_b200 import vren
-    import torch as _t
-    o, d, _ = dev[0]
-    from radnerf_b200.models._render_core import intersect_scene_box
-    hits = intersect_scene_box(tr.model, o, d)[:, 0].contiguous()
-    Ns = []
-    for i in range(K):
-        bf = getattr(tr.model, "density_bitfield" if K == 1 else f"density_bitfield_{i}")
-        out = vren.raymarching_train(o, d, hits, bf, tr.model.cascades, w["scale"], tr.exp_step_factor,
-                                     _t.rand(BATCH, device="cuda"), 128, 1024)
-        Ns.append(int(out[5][0]))
-    N_avg = float(np.mean(Ns))
-    top_t, top_name, top_calls = kern[0]
-    per_launch_ms = top_t / top_calls
-    if top_name in ALGO_FLOPS:
-        achieved = ALGO_FLOPS[top_name] * N_avg / (per_launch_ms * 1e-3) / 1e12
-        roof = {"kernel": top_name, "bound": "tensor", "achieved": achieved, "peak": tflops, "unit": "TFLOP/s",
-                "frac": achieved / tflops, "traffic": None, "peak_source": which}
-    else:
-        f = ALGO_BYTES.get(top_name, lambda N, R: 0)
-        achieved = f(N_avg, BATCH) / (per_launch_ms * 1e-3) / 1e9
-        roof = {"kernel": top_name, "bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                "frac": achieved / hbm, "traffic": None, "peak_source": which}
-    roof["share_of_step"] = top_t / args.steps / ms_step
-    roof["kernel_ms_per_step"] = {n: round(t / args.steps, 4) for t, n, _ in kern}
-    roof["our_kernels_share_of_step"] = total_kernel_ms / args.steps / ms_step
     line = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16 (fp32 accumulate; fp32 march/composite)", "data": "synthetic",
             "config": {"workload": args.workload, "K": K, "scale": w["scale"], "batch_rays_per_gpu": BATCH,
-                       "samples_per_ray": N_avg / BATCH, "params": "tcnn-style random init",
+                       "params": "tcnn-style random init",
                        "occupancy": "analytic scene, fixed; grid update every 16 steps runs on shadow grids",
-                       "l2": "flushed between steps (256 MiB write, its time subtracted)", "parallelism": f"ray-sharded dp{world}"},
+                       "l2": "flushed between steps (256 MiB write, its time subtracted)", "parallelism": f"ray-sharded dp{world}",
+                       "path": "fused engine (rnb_engine_*)" if tr.engine is not None else "python operator surface"},
             "clocks": clk,
             "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * BATCH * 12, "d2h_bytes_per_step": 4,
                     "ms_per_step": e2e_ms},
-            "gpu_launches": launches, "roofline": roof, "final_loss": losses[-1] if losses else None}
+            "gpu_launches": launches, "final_loss": losses[-1] if losses else None}
+    if tr.engine is not None:
+        counts, overflow = tr.engine.sample_stats()
+        N = float(sum(counts)); KR = float(K * BATCH); Pn = float(tr.engine.n_params)
+        line["config"]["samples_per_ray"] = N / KR
+        line["config"]["sample_overflow"] = overflow
+        top = max(stage_ms, key=lambda k: stage_ms[k][0] * stage_ms[k][1])
+        t_ms = stage_ms[top][0]
+        fb = STAGE_BYTES.get(top, lambda *a: 0)(N, KR, Pn) / (t_ms * 1e-3) / 1e9
+        ff = STAGE_FLOPS.get(top, lambda *a: 0)(N, KR, Pn) / (t_ms * 1e-3) / 1e12
+        if ff / tflops > fb / hbm:
+            roof = {"kernel": top, "bound": "tensor", "achieved": ff, "peak": tflops, "unit": "TFLOP/s", "frac": ff / tflops}
+        else:
+            roof = {"kernel": top, "bound": "hbm", "achieved": fb, "peak": hbm, "unit": "GB/s", "frac": fb / hbm}
+        roof.update({"traffic": None, "peak_source": which, "hbm_frac": fb / hbm, "tensor_frac": ff / tflops,
+                     "launch_ms": t_ms, "share_of_step": t_ms * stage_ms[top][1] / args.steps / ms_step,
+                     "stage_ms_per_launch": {k: round(v[0], 4) for k, v in stage_ms.items()},
+                     "stages_share_of_step": sum(v[0] * v[1] for v in stage_ms.values()) / args.steps / ms_step})
+        line["roofline"] = roof
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
     print(json.dumps(line))
@@ -306,6 +309,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="radnerf_tat_k2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--python-surface", action="store_true", help="time the drop-in Python operator surface instead of the fused engine")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -319,6 +319,13 @@ int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float
                     int64_t n, float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                     rnb_stream_t stream);
 
+/* Optional per-stage device timing of the fused step (CUDA events around every stage; off by default).
+ * Stage order: gate, march, scan, expand, field_fwd, composite_fw, blend_loss, composite_bw, field_bwd,
+ * gate_bwd, adam.  rnb_engine_profile_read synchronises, returns the accumulated milliseconds and call
+ * counts since the previous read (arrays of n >= 11 entries) and clears them. */
+int rnb_engine_profile(int enable);
+int rnb_engine_profile_read(double* ms, int32_t* calls, int n);
+
 #ifdef __cplusplus
 }
 #endif

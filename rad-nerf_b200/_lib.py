@@ -44,6 +44,7 @@ def lib() -> ctypes.CDLL:
             fn = getattr(_lib, name)  # raises AttributeError if the header and the .so disagree
             if name not in ("rnb_last_error",):
                 fn.restype = ctypes.c_int
+        _lib.rnb_engine_profile_read.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     return _lib
 
 
@@ -73,7 +74,8 @@ def stream_arg(device=None):
 
 
 # kernels launched per C-ABI call (for bench.py's `gpu_launches` claim)
-KERNELS_PER_CALL = {"rnb_raymarching_train_count": 2}
+KERNELS_PER_CALL = {"rnb_raymarching_train_count": 2, "rnb_engine_gate": 3, "rnb_engine_fwd_bwd": 9, "rnb_engine_adam": 1,
+                    "rnb_engine_layout_of": 0}
 launch_count = 0
 _prof = None
 

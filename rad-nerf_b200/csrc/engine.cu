@@ -374,6 +374,26 @@ __global__ void __launch_bounds__(256) eng_adam_kernel(float* __restrict__ p, __
 
 using namespace rnb;
 
+// ---- optional per-stage device timing (bench.py's roofline leg; off by default) -------------------------
+#include <vector>
+namespace {
+enum Stage { ST_GATE = 0, ST_MARCH, ST_SCAN, ST_EXPAND, ST_FIELD_FWD, ST_COMP_FW, ST_BLEND, ST_COMP_BW, ST_FIELD_BW, ST_GATE_BW, ST_ADAM, ST_COUNT };
+struct ProfRec { int stage; cudaEvent_t a, b; };
+std::vector<ProfRec> g_prof;
+bool g_prof_on = false;
+struct StageTimer {
+  cudaStream_t st; cudaEvent_t b = nullptr;
+  StageTimer(int stage, cudaStream_t s) : st(s) {
+    if (!g_prof_on) return;
+    ProfRec r; r.stage = stage;
+    cudaEventCreate(&r.a); cudaEventCreate(&r.b);
+    cudaEventRecord(r.a, st);
+    b = r.b; g_prof.push_back(r);
+  }
+  ~StageTimer() { if (b) cudaEventRecord(b, st); }
+};
+}  // namespace
+
 static int check_cfg(const rnb_engine_config* c, const char* what) {
   RNB_REQUIRE(c != nullptr, what);
   RNB_REQUIRE(c->K >= 1 && c->K <= RNB_MAX_K && c->n_rays >= 1 && c->max_samples >= 1 && c->max_samples <= 65536, what);
@@ -423,6 +443,7 @@ int rnb_engine_gate(const rnb_engine_config* c, void* workspace, const void* par
   char* ws = (char*)workspace;
   cudaStream_t st = as_stream(stream);
   const int R = c->n_rays;
+  StageTimer tm(ST_GATE, st);
   __half* gate_in = (__half*)(ws + L.gate_in);
   eng_gate_in_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, gate_in);
   const __half* gw = (const __half*)params_f16 + c->gate_off;
@@ -460,14 +481,17 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
   BitfieldPtrs bf;
   for (int i = 0; i < K; i++) { RNB_REQUIRE(bitfields[i] != nullptr, what); bf.p[i] = bitfields[i]; }
   const dim3 ray_grid(ceil_div((int64_t)R * 32, 256), K);
+  {
+  StageTimer tm(ST_MARCH, st);
   if (c->exp_step_factor == 0.0f)
     eng_march_kernel<true><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2],
                                                      c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch);
   else
     eng_march_kernel<false><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2],
                                                       c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch);
-  eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg);
-  eng_expand_kernel<<<ray_grid, 256, 0, st>>>(counts, starts, t_scratch, mp, R, S, ray_id, ts, deltas);
+  }
+  { StageTimer tm(ST_SCAN, st); eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg); }
+  { StageTimer tm(ST_EXPAND, st); eng_expand_kernel<<<ray_grid, 256, 0, st>>>(counts, starts, t_scratch, mp, R, S, ray_id, ts, deltas); }
   if (int rc = check_launch(what)) return rc;
   // 4. field forward
   rnb_field_params P;
@@ -477,11 +501,12 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
   for (int i = 0; i < K; i++) { P.geo_w_f16[i] = p16 + c->geo_off[i]; P.rgb_w_f16[i] = p16 + c->rgb_off[i]; }
   rnb_samples Sm = {rays_o, rays_d, ray_id, ts, seg, S};
   rnb_field_saved Sv = {ws + L.enc, ws + L.rgb_in, ws + L.geo_h, ws + L.rgb_h1, ws + L.rgb_h2, ws + L.sraw};
-  if (int rc = rnb_field_fwd(&P, &Sm, with_backward ? &Sv : nullptr, sigmas, rgb4, stream)) return rc;
+  { StageTimer tm(ST_FIELD_FWD, st); if (int rc = rnb_field_fwd(&P, &Sm, with_backward ? &Sv : nullptr, sigmas, rgb4, stream)) return rc; }
   // 5. composite, 6. blend + loss + gradient seeds
   float* p_op = (float*)(ws + L.pass_opacity); float* p_de = (float*)(ws + L.pass_depth); float* p_rgb = (float*)(ws + L.pass_rgb);
+  { StageTimer tm(ST_COMP_FW, st);
   eng_composite_fw_kernel<<<ray_grid, 256, 0, st>>>(sigmas, rgb4, deltas, ts, counts, starts, c->T_threshold, R, S, wsamp, p_op, p_de, p_rgb,
-                                                    (int32_t*)(ws + L.pass_total));
+                                                    (int32_t*)(ws + L.pass_total)); }
   BlendArgs B;
   B.n_rays = R; B.K = K; B.inv_rays_global = 1.0f / (float)n_rays_global;
   B.lambda_opacity = c->lambda_opacity; B.lambda_cv = c->lambda_cv; B.lambda_dm = c->lambda_dm; B.gs = c->loss_scale;
@@ -491,18 +516,21 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
   B.rgb = (float*)(ws + L.rgb); B.opacity = (float*)(ws + L.opacity); B.depth = (float*)(ws + L.depth);
   B.d_opacity = (float*)(ws + L.d_pass_opacity); B.d_depth = (float*)(ws + L.d_pass_depth); B.d_rgb = (float*)(ws + L.d_pass_rgb);
   B.dlogits = (__half*)(ws + L.gate_dlogits); B.loss = (float*)(ws + L.loss); B.with_backward = with_backward;
-  eng_blend_loss_kernel<<<ceil_div(R, 256), 256, 0, st>>>(B);
+  { StageTimer tm(ST_BLEND, st); eng_blend_loss_kernel<<<ceil_div(R, 256), 256, 0, st>>>(B); }
   if (int rc = check_launch(what)) return rc;
   if (!with_backward) return RNB_OK;
   // 7. backward: composite, field, gate
   float* dsig = (float*)(ws + L.dsigmas); float* drgb = (float*)(ws + L.drgbs);
+  { StageTimer tm(ST_COMP_BW, st);
   eng_composite_bw_kernel<<<ray_grid, 256, 0, st>>>(sigmas, rgb4, deltas, ts, counts, starts, c->T_threshold, R, S, p_op, p_de, p_rgb,
-                                                    B.d_opacity, B.d_depth, B.d_rgb, dsig, drgb);
+                                                    B.d_opacity, B.d_depth, B.d_rgb, dsig, drgb); }
   if (int rc = check_launch(what)) return rc;
   float* gg[RNB_MAX_K]; float* gr[RNB_MAX_K];
   for (int i = 0; i < K; i++) { gg[i] = grads_f32 + c->geo_off[i]; gr[i] = grads_f32 + c->rgb_off[i]; }
-  if (int rc = rnb_field_bwd(&P, &Sm, &Sv, rgb4, dsig, drgb, c->loss_scale, grads_f32 + c->table_off, gg, gr, stream)) return rc;
+  { StageTimer tm(ST_FIELD_BW, st);
+  if (int rc = rnb_field_bwd(&P, &Sm, &Sv, rgb4, dsig, drgb, c->loss_scale, grads_f32 + c->table_off, gg, gr, stream)) return rc; }
   if (K > 1) {
+    StageTimer tm(ST_GATE_BW, st);
     if (int rc = rnb_mlp_bwd(&kGateDesc, p16 + c->gate_off, ws + L.gate_in, ws + L.gate_hidden, ws + L.gate_logits, ws + L.gate_dlogits,
                              R, nullptr, grads_f32 + c->gate_off, 1.0f / c->loss_scale, stream)) return rc;
   }
@@ -520,9 +548,31 @@ int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float
   int64_t blocks = (n / 4 + 255) / 256;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
   if (blocks < 1) blocks = 1;
+  StageTimer tm(ST_ADAM, as_stream(stream));
   eng_adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(params_f32, (__half*)params_f16, grads_f32, exp_avg, exp_avg_sq, n, step_size,
                                                               beta1, beta2, eps, inv_sqrt_bc2, grad_scale);
   return check_launch(what);
+}
+
+
+int rnb_engine_profile(int enable) {
+  g_prof_on = enable != 0;
+  return RNB_OK;
+}
+
+/* ms[ST_COUNT], calls[ST_COUNT]: device time and number of timed stages since the last read (synchronises). */
+int rnb_engine_profile_read(double* ms, int32_t* calls, int n) {
+  const char* what = "rnb_engine_profile_read";
+  RNB_REQUIRE(ms && calls && n >= ST_COUNT, what);
+  for (int i = 0; i < n; i++) { ms[i] = 0.0; calls[i] = 0; }
+  for (auto& r : g_prof) {
+    cudaEventSynchronize(r.b);
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { ms[r.stage] += t; calls[r.stage]++; }
+    cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  return RNB_OK;
 }
 
 }  // extern "C"

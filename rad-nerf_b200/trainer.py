@@ -25,7 +25,7 @@ from .models.rendering import render
 class Trainer:
     def __init__(self, scale=0.5, K=2, lr=1e-2, log2_T=19, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
                  loss_scale=1024.0, device="cuda", update_interval=16, warmup_steps=256, freeze_occupancy=False,
-                 random_bg=False, seed=0):
+                 random_bg=False, seed=0, engine=True, batch_rays=8192, samples_per_ray=128):
         self.device = torch.device(device)
         self.K, self.scale = K, scale
         self.exp_step_factor = syn.exp_step_factor_for_scale(scale)
@@ -49,6 +49,14 @@ class Trainer:
         self.global_step = 0
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         self._shadow = None
+        self.lr = lr
+        self.engine = None
+        if engine:
+            # the fused step (csrc/engine.cu): same modules, their parameters re-homed into one flat vector
+            from .engine import Engine
+            self.engine = Engine(self.model, self.gate, n_rays=batch_rays, exp_step_factor=self.exp_step_factor,
+                                 samples_per_ray=samples_per_ray, lambda_opacity=lambda_opacity, lambda_cv=lambda_cv,
+                                 lambda_dm=lambda_dm, lr=lr)
 
     # -- occupancy ---------------------------------------------------------------------------
     def set_occupancy(self, bitfields):
@@ -83,6 +91,11 @@ class Trainer:
         """rays_o, rays_d, target_rgb: (B_local,3) fp32 CUDA tensors.  Returns the (unscaled) loss tensor."""
         if self.global_step % self.update_interval == 0:
             self._grid_update()
+        if self.engine is not None:
+            loss = self.engine.step(rays_o, rays_d, target_rgb, lr=self.lr, random_bg=self.random_bg)
+            self.global_step += 1
+            self.last_results = self.engine.results()
+            return loss[0]
         kw = dict(test_time=False, random_bg=self.random_bg)
         if self.exp_step_factor:
             kw["exp_step_factor"] = self.exp_step_factor
