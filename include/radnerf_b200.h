@@ -326,6 +326,12 @@ int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float
 int rnb_engine_profile(int enable);
 int rnb_engine_profile_read(double* ms, int32_t* calls, int n);
 
+/* Diagnostics: self-test of the tcgen05 building blocks (csrc/tc05.cuh) on one CTA.
+ * X (128,64), W (64,64), Y (128,32) f16 row-major -> out1 (128,64) = X W^T, out2 (128,32) = raw TMEM
+ * dump (128 lanes) of the M=64 product X^T Y, out3 (128,64) = X W.  f32 outputs. */
+int rnb_tc_probe(const void* X, const void* W, const void* Y, float* out1, float* out2, float* out3,
+                 rnb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
