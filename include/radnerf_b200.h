@@ -326,6 +326,11 @@ int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float
 int rnb_engine_profile(int enable);
 int rnb_engine_profile_read(double* ms, int32_t* calls, int n);
 
+/* Selects the implementation behind rnb_field_fwd / rnb_field_bwd: 1 = tcgen05 + TMEM kernels
+ * (csrc/field_tc.cu, default where available), 0 = mma.sync register-chained kernels (csrc/field.cu).
+ * Both compute the same operator; the switch exists for A/B measurement and parity tests. */
+int rnb_set_field_impl(int fwd_tcgen05, int bwd_tcgen05);
+
 /* Diagnostics: self-test of the tcgen05 building blocks (csrc/tc05.cuh) on one CTA.
  * X (128,64), W (64,64), Y (128,32) f16 row-major -> out1 (128,64) = X W^T, out2 (128,32) = raw TMEM
  * dump (128 lanes) of the M=64 product X^T Y, out3 (128,64) = X W.  f32 outputs. */

@@ -553,7 +553,21 @@ static int field_grid(int64_t capacity, int per_sm) {
   return (int)(tiles < cap ? tiles : cap);
 }
 
+int rnb_field_fwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, float* sigmas,
+                            void* rgb4_f16, rnb_stream_t stream);
+int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, const void* rgb4_f16,
+                            const float* dL_dsigmas, const float* dL_drgbs, float loss_scale, float* grad_table,
+                            float* const* grad_geo, float* const* grad_rgb, rnb_stream_t stream);
+static int g_fwd_impl = 1;   // 1 = tcgen05 (field_tc.cu), 0 = mma.sync (this file)
+static int g_bwd_impl = 0;
+
 extern "C" {
+
+int rnb_set_field_impl(int fwd_tcgen05, int bwd_tcgen05) {
+  g_fwd_impl = fwd_tcgen05 ? 1 : 0;
+  g_bwd_impl = bwd_tcgen05 ? 1 : 0;
+  return RNB_OK;
+}
 
 int rnb_field_fwd(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, float* sigmas,
                   void* rgb4_f16, rnb_stream_t stream) {
@@ -562,6 +576,8 @@ int rnb_field_fwd(const rnb_field_params* P, const rnb_samples* S, const rnb_fie
   if (int rc = make_field_args(P, S, &A, what)) return rc;
   RNB_REQUIRE(sigmas && rgb4_f16, what);
   const bool save = saved != nullptr && saved->enc != nullptr;
+  if (save) RNB_REQUIRE(saved->rgb_in && saved->geo_h && saved->rgb_h1 && saved->rgb_h2 && saved->sraw, what);
+  if (g_fwd_impl == 1) return rnb_field_fwd_tc_launch(P, S, saved, sigmas, rgb4_f16, stream);
   const int grid = field_grid(S->capacity, 4);
   if (save) {
     RNB_REQUIRE(saved->rgb_in && saved->geo_h && saved->rgb_h1 && saved->rgb_h2 && saved->sraw, what);

@@ -1,0 +1,309 @@
+// field_tc.cu -- the fused field on Blackwell's 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// Same operator as field.cu's field_fwd_kernel (hash-grid encode -> geo MLP -> TruncExp -> SH4 ->
+// rgb MLP for all K passes of a packed sample list), re-mapped for sm_100a:
+//   * one persistent CTA per SM, kWG warpgroups; a warpgroup owns one 128-sample tile at a time and
+//     THREAD = SAMPLE everywhere: the thread gathers its 16x8 table entries, writes its 32 encoded
+//     features as four 16-byte chunks straight into the canonical (no-swizzle) K-major operand tile in
+//     shared memory, and later reads back ITS row of every layer's accumulator from tensor memory
+//     (tcgen05.ld 32x32b: TMEM lane = tile row = thread), applies ReLU / TruncExp / sigmoid, and
+//     writes the fp16 row as the next layer's operand.  No mma.sync fragment layouts, no shuffles, no
+//     transposition through shared memory; accumulators never occupy registers.
+//   * the five dense layers are tcgen05.mma (M = 128, N = 64/32/64/64/16, K = 16 per instruction),
+//     issued by one elected thread of the warpgroup, completion signalled through an mbarrier
+//     (tcgen05.commit); the 22 KB of weights of the current pass are staged once per pass and CTA.
+//   * while one warpgroup waits for its MMA or its gathers, the other warpgroups of the SM are in other
+//     phases of their own tiles (gather is L2-latency bound, the layer chain is a dependent sequence).
+// Rounding points are those of the operator path (fp16 features / activations / outputs, fp32
+// accumulation), so this kernel, field.cu and radnerf_b200.tcnn agree to fp16 resolution.
+#include "hashgrid.cuh"
+#include "tc05.cuh"
+
+namespace rnb {
+
+constexpr int kWG = 4;            // warpgroups per CTA (forward)
+constexpr int kRows = 128;        // samples per tile
+
+struct TcFieldArgs {
+  GridLevels g;
+  float xmin[3], xden[3];
+  const __half2* table;
+  const __half* geo_w[RNB_MAX_K];
+  const __half* rgb_w[RNB_MAX_K];
+  int K;
+  const float* rays_o; const float* rays_d;
+  const int32_t* ray_id; const float* ts; const int32_t* seg;
+  int64_t capacity;
+};
+
+__device__ __forceinline__ uint32_t pack2h(float a, float b) {
+  const __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// one level of the multiresolution grid -> packed half2 (same arithmetic as hashgrid_fwd_kernel)
+__device__ __forceinline__ uint32_t tc_encode_level(const TcFieldArgs& A, int l, float x, float y, float z) {
+  const uint32_t res = A.g.res[l], off = A.g.offset[l], size = A.g.offset[l + 1] - off;
+  const bool dense = level_is_dense(res, size);
+  const Corner c = locate(x, y, z, A.g.scale[l]);
+  const __half2* t = A.table + off;
+  __half2 v[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const uint32_t idx = grid_index(c.cx + (k & 1), c.cy + ((k >> 1) & 1), c.cz + (k >> 2), res, size, dense);
+    v[k] = __ldg(t + idx);
+  }
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const float w = ((k & 1) ? c.wx : 1.f - c.wx) * (((k >> 1) & 1) ? c.wy : 1.f - c.wy) * ((k >> 2) ? c.wz : 1.f - c.wz);
+    const float2 f = __half22float2(v[k]);
+    a0 = fmaf(w, f.x, a0); a1 = fmaf(w, f.y, a1);
+  }
+  return pack2h(a0, a1);
+}
+
+// W (n_out, n_in) row-major fp16 in global -> canonical K-major tile [n_out rows][n_in features] in smem
+__device__ __forceinline__ void tc_stage_weight(unsigned char* dst, const __half* __restrict__ src, int n_out, int n_in, int tid, int nthreads) {
+  const int cpr = n_in / 8;
+  for (int i = tid; i < n_out * cpr; i += nthreads) {
+    const int n = i / cpr, c = i % cpr;
+    *reinterpret_cast<uint4*>(dst + tc::tile_chunk_off(n_out, n, c)) = __ldg(reinterpret_cast<const uint4*>(src + n * n_in) + c);
+  }
+}
+
+struct TcSmem {
+  // weights of the current pass (bytes)
+  static constexpr int g1 = 0;                 // 64 x 32
+  static constexpr int g2 = g1 + 64 * 32 * 2;  // 32 x 64
+  static constexpr int r1 = g2 + 32 * 64 * 2;  // 64 x 32
+  static constexpr int r2 = r1 + 64 * 32 * 2;  // 64 x 64
+  static constexpr int r3 = r2 + 64 * 64 * 2;  // 16 x 64
+  static constexpr int wend = r3 + 16 * 64 * 2;
+  // per warpgroup: a 128x32 operand tile (encoding, then rgb input) and a 128x64 tile (hidden activations)
+  static constexpr int a8 = 0;
+  static constexpr int b16 = kRows * 32 * 2;
+  static constexpr int per_wg = b16 + kRows * 64 * 2;
+  static constexpr int wg0 = (wend + 127) / 128 * 128;
+  static constexpr int bars = wg0 + kWG * per_wg;       // kWG mbarriers
+  static constexpr int tmem_slot = bars + kWG * 8;
+  static constexpr int bytes = tmem_slot + 16;
+};
+
+// D[tmem] = A[128 x KDIM] * W[N x KDIM]^T, issued by one thread
+template <int N, int KDIM>
+__device__ __forceinline__ void tc_layer_mma(uint32_t d_tmem, uint32_t a_smem, uint32_t w_smem) {
+  constexpr uint32_t idesc = tc::instr_desc(128, N, 0, 0);
+#pragma unroll
+  for (int k = 0; k < KDIM / 16; k++)
+    tc::mma_f16(d_tmem, tc::smem_desc(a_smem + k * 2 * (kRows * 16), kRows * 16, 128), tc::smem_desc(w_smem + k * 2 * (N * 16), N * 16, 128), idesc, k > 0);
+}
+
+// named barrier over the 128 threads of a warpgroup (barrier ids 1..kWG; 0 is __syncthreads)
+__device__ __forceinline__ void wg_sync(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(wg + 1) : "memory"); }
+
+// 64 accumulator columns of this thread's row -> ReLU -> fp16 -> 8 operand chunks (+ optional global row)
+__device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* tile, int row, __half* __restrict__ save_row) {
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    uint32_t r[32];
+    tc::tmem_ld32_nowait(taddr + h * 32, r);
+    tc::tmem_ld_wait();
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      uint4 q;
+      q.x = pack2h(fmaxf(__uint_as_float(r[8 * c + 0]), 0.f), fmaxf(__uint_as_float(r[8 * c + 1]), 0.f));
+      q.y = pack2h(fmaxf(__uint_as_float(r[8 * c + 2]), 0.f), fmaxf(__uint_as_float(r[8 * c + 3]), 0.f));
+      q.z = pack2h(fmaxf(__uint_as_float(r[8 * c + 4]), 0.f), fmaxf(__uint_as_float(r[8 * c + 5]), 0.f));
+      q.w = pack2h(fmaxf(__uint_as_float(r[8 * c + 6]), 0.f), fmaxf(__uint_as_float(r[8 * c + 7]), 0.f));
+      *reinterpret_cast<uint4*>(tile + tc::tile_chunk_off(kRows, row, h * 4 + c)) = q;
+      if (save_row) reinterpret_cast<uint4*>(save_row)[h * 4 + c] = q;
+    }
+  }
+}
+
+template <bool kSave>
+__global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs A, __half* __restrict__ s_enc, __half* __restrict__ s_rgb_in,
+                                                                     __half* __restrict__ s_geo_h, __half* __restrict__ s_rgb_h1,
+                                                                     __half* __restrict__ s_rgb_h2, __half* __restrict__ s_sraw,
+                                                                     float* __restrict__ sigmas, __half* __restrict__ rgb4) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, wg = tid >> 7, row = tid & 127, warp = tid >> 5;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcSmem::tmem_slot);
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+  if (tid < kWG) tc::mbar_init(bars + tid, 1);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_d = *tmem_slot + wg * 64;                               // this warpgroup's 64 accumulator columns
+  const uint32_t tmem_row = tmem_d + ((uint32_t)((warp & 3) * 32) << 16);     // + this warp's 32 lanes
+  unsigned char* a8 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::a8;
+  unsigned char* b16 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::b16;
+  const uint32_t a8_s = tc::smem_u32(a8), b16_s = tc::smem_u32(b16), w_s = tc::smem_u32(smem);
+  uint64_t* bar = bars + wg;
+  uint32_t phase = 0;
+  const int K = A.K;
+  for (int pass = 0; pass < K; pass++) {
+    const int64_t base = __ldg(A.seg + pass);
+    int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
+    if (pass_end > A.capacity) pass_end = A.capacity;
+    const int64_t n_tiles = pass_end > base ? (pass_end - base + kRows - 1) / kRows : 0;
+    // ---- stage this pass's weights (whole CTA) ----
+    __syncthreads();
+    {
+      const __half* gw = A.geo_w[pass];
+      const __half* rw = A.rgb_w[pass];
+      tc_stage_weight(smem + TcSmem::g1, gw, 64, 32, tid, kWG * 128);
+      tc_stage_weight(smem + TcSmem::g2, gw + 64 * 32, 32, 64, tid, kWG * 128);
+      tc_stage_weight(smem + TcSmem::r1, rw, 64, 32, tid, kWG * 128);
+      tc_stage_weight(smem + TcSmem::r2, rw + 64 * 32, 64, 64, tid, kWG * 128);
+      tc_stage_weight(smem + TcSmem::r3, rw + 64 * 32 + 64 * 64, 16, 64, tid, kWG * 128);
+    }
+    tc::fence_async_smem();
+    __syncthreads();
+    for (int64_t tile = (int64_t)blockIdx.x * kWG + wg; tile < n_tiles; tile += (int64_t)gridDim.x * kWG) {
+      const int64_t s = base + tile * kRows + row;
+      const bool valid = s < pass_end;
+      // ---- gather: 16 levels x 8 corners -> 32 fp16 features -> operand tile (4 chunks) ----
+      uint4 shq0 = make_uint4(0u, 0u, 0u, 0u), shq1 = shq0;
+      if (valid) {
+        const int r = __ldg(A.ray_id + s);
+        const float t = __ldg(A.ts + s);
+        const float ox = __ldg(A.rays_o + 3 * r), oy = __ldg(A.rays_o + 3 * r + 1), oz = __ldg(A.rays_o + 3 * r + 2);
+        const float dx = __ldg(A.rays_d + 3 * r), dy = __ldg(A.rays_d + 3 * r + 1), dz = __ldg(A.rays_d + 3 * r + 2);
+        const float x = fminf(fmaxf(__fdiv_rn(__fmaf_rn(dx, t, ox) - A.xmin[0], A.xden[0]), 0.f), 1.f);
+        const float y = fminf(fmaxf(__fdiv_rn(__fmaf_rn(dy, t, oy) - A.xmin[1], A.xden[1]), 0.f), 1.f);
+        const float z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(dz, t, oz) - A.xmin[2], A.xden[2]), 0.f), 1.f);
+#pragma unroll 1
+        for (int c = 0; c < 4; c++) {
+          uint4 q;
+          q.x = tc_encode_level(A, 4 * c, x, y, z); q.y = tc_encode_level(A, 4 * c + 1, x, y, z);
+          q.z = tc_encode_level(A, 4 * c + 2, x, y, z); q.w = tc_encode_level(A, 4 * c + 3, x, y, z);
+          *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, c)) = q;
+          if (kSave) reinterpret_cast<uint4*>(s_enc + s * 32)[c] = q;
+        }
+        // direction: d/|d| -> (d+1)/2 -> (tcnn) 2u-1 -> SH4   (networks.py:322-323)
+        const float nrm = sqrtf(dx * dx + dy * dy + dz * dz);
+        const float ux = (__fdiv_rn(dx, nrm) + 1.f) * 0.5f, uy = (__fdiv_rn(dy, nrm) + 1.f) * 0.5f, uz = (__fdiv_rn(dz, nrm) + 1.f) * 0.5f;
+        float o[16];
+        sh4_eval(ux * 2.f - 1.f, uy * 2.f - 1.f, uz * 2.f - 1.f, o);
+        shq0 = make_uint4(pack2h(o[0], o[1]), pack2h(o[2], o[3]), pack2h(o[4], o[5]), pack2h(o[6], o[7]));
+        shq1 = make_uint4(pack2h(o[8], o[9]), pack2h(o[10], o[11]), pack2h(o[12], o[13]), pack2h(o[14], o[15]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; c++) *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, c)) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      // ---- geo layer 1: 32 -> 64, ReLU ----
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<64, 32>(tmem_d, a8_s, w_s + TcSmem::g1); tc::mma_commit(bar); }
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      tc_relu_row64(tmem_row, b16, row, (kSave && valid) ? s_geo_h + s * 64 : nullptr);
+      // ---- geo layer 2: 64 -> 32 (col 0 = raw sigma, cols 1..16 = geometry feature) ----
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<32, 64>(tmem_d, b16_s, w_s + TcSmem::g2); tc::mma_commit(bar); }
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      {
+        uint32_t r[32];
+        tc::tmem_ld32_nowait(tmem_row, r);
+        tc::tmem_ld_wait();
+        const __half raw = __float2half_rn(__uint_as_float(r[0]));
+        uint4 f0, f1;
+        f0.x = pack2h(__uint_as_float(r[1]), __uint_as_float(r[2])); f0.y = pack2h(__uint_as_float(r[3]), __uint_as_float(r[4]));
+        f0.z = pack2h(__uint_as_float(r[5]), __uint_as_float(r[6])); f0.w = pack2h(__uint_as_float(r[7]), __uint_as_float(r[8]));
+        f1.x = pack2h(__uint_as_float(r[9]), __uint_as_float(r[10])); f1.y = pack2h(__uint_as_float(r[11]), __uint_as_float(r[12]));
+        f1.z = pack2h(__uint_as_float(r[13]), __uint_as_float(r[14])); f1.w = pack2h(__uint_as_float(r[15]), __uint_as_float(r[16]));
+        // rgb input = [SH4 | geometry feature]; the 128x32 tile is free again (its MMA completed)
+        *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, 0)) = shq0;
+        *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, 1)) = shq1;
+        *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, 2)) = f0;
+        *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, 3)) = f1;
+        if (valid) {
+          sigmas[s] = expf(__half2float(raw));
+          if (kSave) {
+            s_sraw[s] = raw;
+            uint4* dst = reinterpret_cast<uint4*>(s_rgb_in + s * 32);
+            dst[0] = shq0; dst[1] = shq1; dst[2] = f0; dst[3] = f1;
+          }
+        }
+      }
+      // ---- rgb layer 1: 32 -> 64, ReLU ----
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<64, 32>(tmem_d, a8_s, w_s + TcSmem::r1); tc::mma_commit(bar); }
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      tc_relu_row64(tmem_row, b16, row, (kSave && valid) ? s_rgb_h1 + s * 64 : nullptr);
+      // ---- rgb layer 2: 64 -> 64, ReLU ----
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<64, 64>(tmem_d, b16_s, w_s + TcSmem::r2); tc::mma_commit(bar); }
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      tc_relu_row64(tmem_row, b16, row, (kSave && valid) ? s_rgb_h2 + s * 64 : nullptr);
+      // ---- rgb layer 3: 64 -> 16, sigmoid ----
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<16, 64>(tmem_d, b16_s, w_s + TcSmem::r3); tc::mma_commit(bar); }
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      {
+        float v[16];
+        tc::tmem_ld16(tmem_row, v);
+        if (valid) {
+          const uint2 q = make_uint2(pack2h(1.f / (1.f + __expf(-v[0])), 1.f / (1.f + __expf(-v[1]))),
+                                     pack2h(1.f / (1.f + __expf(-v[2])), 1.f / (1.f + __expf(-v[3]))));
+          *reinterpret_cast<uint2*>(rgb4 + s * 4) = q;
+        }
+      }
+      tc::fence_before_sync();   // the next tile's first MMA overwrites the accumulator columns just read
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+}
+
+}  // namespace rnb
+
+using namespace rnb;
+
+int rnb_field_fwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, float* sigmas,
+                            void* rgb4_f16, rnb_stream_t stream) {
+  const char* what = "rnb_field_fwd(tcgen05)";
+  TcFieldArgs A;
+  RNB_REQUIRE(P != nullptr && S != nullptr && P->K >= 1 && P->K <= RNB_MAX_K && P->grid.n_levels == 16, what);
+  if (int rc = to_levels(&P->grid, &A.g, what)) return rc;
+  for (int c = 0; c < 3; c++) { A.xmin[c] = P->xyz_min[c]; A.xden[c] = P->xyz_max[c] - P->xyz_min[c]; }
+  A.table = (const __half2*)P->table_f16;
+  for (int i = 0; i < P->K; i++) { A.geo_w[i] = (const __half*)P->geo_w_f16[i]; A.rgb_w[i] = (const __half*)P->rgb_w_f16[i]; }
+  A.K = P->K;
+  A.rays_o = S->rays_o; A.rays_d = S->rays_d; A.ray_id = S->ray_id; A.ts = S->ts; A.seg = S->seg; A.capacity = S->capacity;
+  const bool save = saved != nullptr && saved->enc != nullptr;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RNB_CUDA(cudaFuncSetAttribute(field_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem::bytes), what);
+    RNB_CUDA(cudaFuncSetAttribute(field_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem::bytes), what);
+    attr_set = true;
+  }
+  const int64_t tiles = S->capacity / kRows;
+  int grid = (int)((tiles + kWG - 1) / kWG);
+  if (grid > kNumSMs) grid = kNumSMs;
+  if (save)
+    field_fwd_tc_kernel<true><<<grid, kWG * 128, TcSmem::bytes, as_stream(stream)>>>(A, (__half*)saved->enc, (__half*)saved->rgb_in, (__half*)saved->geo_h,
+                                                                                    (__half*)saved->rgb_h1, (__half*)saved->rgb_h2, (__half*)saved->sraw,
+                                                                                    sigmas, (__half*)rgb4_f16);
+  else
+    field_fwd_tc_kernel<false><<<grid, kWG * 128, TcSmem::bytes, as_stream(stream)>>>(A, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, sigmas,
+                                                                                     (__half*)rgb4_f16);
+  return check_launch(what);
+}
