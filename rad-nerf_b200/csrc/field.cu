@@ -494,19 +494,16 @@ __global__ void __launch_bounds__(128) field_bwd_kernel(FieldArgs A, const __hal
       if (active) p = load_sample(A, s);
       const __half2* drow = reinterpret_cast<const __half2*>(dzbuf + (warp * 32 + lane) * 40);
       for (int l = 0; l < A.g.n_levels; l++) {
-        const uint32_t res = A.g.res[l], off = A.g.offset[l], size = A.g.offset[l + 1] - off;
-        const bool dense = level_is_dense(res, size);
-        const Corner c = locate(p.x, p.y, p.z, A.g.scale[l]);
+        const uint32_t off = A.g.offset[l];
+        const LevelCorners L = level_corners(p.x, p.y, p.z, A.g.scale[l], A.g.res[l], A.g.offset[l + 1] - off);
         float2 d = __half22float2(drow[l]);
         d.x *= inv_gs; d.y *= inv_gs;
         float* gl = grad_table + 2 * (size_t)off;
         const bool aggregate = l < n_aggregate_levels;   // warp-uniform
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-          const uint32_t idx = grid_index(c.cx + (k & 1), c.cy + ((k >> 1) & 1), c.cz + (k >> 2), res, size, dense);
-          const float w = ((k & 1) ? c.wx : 1.f - c.wx) * (((k >> 1) & 1) ? c.wy : 1.f - c.wy) * ((k >> 2) ? c.wz : 1.f - c.wz);
-          if (aggregate) scatter_aggregated(gl, idx, w * d.x, w * d.y, active);
-          else if (active) red_add_f32x2(gl + 2 * (size_t)idx, w * d.x, w * d.y);
+          if (aggregate) scatter_aggregated(gl, L.idx[k], L.w[k] * d.x, L.w[k] * d.y, active);
+          else if (active) red_add_f32x2(gl + 2 * (size_t)L.idx[k], L.w[k] * d.x, L.w[k] * d.y);
         }
       }
     }

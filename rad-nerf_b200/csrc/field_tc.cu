@@ -43,22 +43,17 @@ __device__ __forceinline__ uint32_t pack2h(float a, float b) {
 
 // one level of the multiresolution grid -> packed half2 (same arithmetic as hashgrid_fwd_kernel)
 __device__ __forceinline__ uint32_t tc_encode_level(const TcFieldArgs& A, int l, float x, float y, float z) {
-  const uint32_t res = A.g.res[l], off = A.g.offset[l], size = A.g.offset[l + 1] - off;
-  const bool dense = level_is_dense(res, size);
-  const Corner c = locate(x, y, z, A.g.scale[l]);
+  const uint32_t off = A.g.offset[l];
+  const LevelCorners L = level_corners(x, y, z, A.g.scale[l], A.g.res[l], A.g.offset[l + 1] - off);
   const __half2* t = A.table + off;
   __half2 v[8];
 #pragma unroll
-  for (int k = 0; k < 8; k++) {
-    const uint32_t idx = grid_index(c.cx + (k & 1), c.cy + ((k >> 1) & 1), c.cz + (k >> 2), res, size, dense);
-    v[k] = __ldg(t + idx);
-  }
+  for (int k = 0; k < 8; k++) v[k] = __ldg(t + L.idx[k]);
   float a0 = 0.f, a1 = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; k++) {
-    const float w = ((k & 1) ? c.wx : 1.f - c.wx) * (((k >> 1) & 1) ? c.wy : 1.f - c.wy) * ((k >> 2) ? c.wz : 1.f - c.wz);
     const float2 f = __half22float2(v[k]);
-    a0 = fmaf(w, f.x, a0); a1 = fmaf(w, f.y, a1);
+    a0 = fmaf(L.w[k], f.x, a0); a1 = fmaf(L.w[k], f.y, a1);
   }
   return pack2h(a0, a1);
 }

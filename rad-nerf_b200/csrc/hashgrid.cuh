@@ -101,3 +101,51 @@ __device__ __forceinline__ void sh4_eval(float x, float y, float z, float (&o)[1
 }
 
 }  // namespace rnb
+
+namespace rnb {
+
+// ---- lean per-level corner math (shared by the fused field kernels) ----------------------------------
+// The eight corner indices of a cell need only the two candidates per axis: for hashed levels
+// (table size a power of two) idx = (x' ^ y' ^ z') & mask with y' = y*2654435761, z' = z*805459861
+// precomputed for y, y+1 / z, z+1 (one LOP3 + one AND per corner); for dense levels
+// idx = x + y*res + z*res^2 with the y / z terms precomputed (one IADD3 per corner) and a conditional
+// subtract for the single +1 corner that can leave the level on the upper boundary.
+struct LevelCorners {
+  uint32_t idx[8];
+  float w[8];
+};
+
+__device__ __forceinline__ LevelCorners level_corners(float x, float y, float z, float scale, uint32_t res, uint32_t size) {
+  LevelCorners L;
+  const float px = fmaf(scale, x, 0.5f), py = fmaf(scale, y, 0.5f), pz = fmaf(scale, z, 0.5f);
+  const float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+  const uint32_t cx = (uint32_t)(int)fx, cy = (uint32_t)(int)fy, cz = (uint32_t)(int)fz;
+  const float wx1 = px - fx, wy1 = py - fy, wz1 = pz - fz;
+  const float wx0 = 1.f - wx1, wy0 = 1.f - wy1, wz0 = 1.f - wz1;
+  // weight of corner k = (x-term) * (y-term) * (z-term), evaluated in the same order as hashgrid_fwd_kernel
+  const float xy00 = wx0 * wy0, xy10 = wx1 * wy0, xy01 = wx0 * wy1, xy11 = wx1 * wy1;
+  L.w[0] = xy00 * wz0; L.w[1] = xy10 * wz0; L.w[2] = xy01 * wz0; L.w[3] = xy11 * wz0;
+  L.w[4] = xy00 * wz1; L.w[5] = xy10 * wz1; L.w[6] = xy01 * wz1; L.w[7] = xy11 * wz1;
+  if ((uint64_t)res * res * res <= (uint64_t)size) {   // dense level (warp-uniform)
+    const uint32_t y0 = cy * res, y1 = y0 + res, z0 = cz * res * res, z1 = z0 + res * res;
+    const uint32_t b00 = cx + y0 + z0, b01 = cx + y1 + z0, b10 = cx + y0 + z1, b11 = cx + y1 + z1;
+    L.idx[0] = b00; L.idx[1] = b00 + 1; L.idx[2] = b01; L.idx[3] = b01 + 1;
+    L.idx[4] = b10; L.idx[5] = b10 + 1; L.idx[6] = b11; L.idx[7] = b11 + 1;
+#pragma unroll
+    for (int k = 0; k < 8; k++) if (L.idx[k] >= size) L.idx[k] -= size;
+  } else if ((size & (size - 1u)) == 0u) {             // hashed, power-of-two table
+    const uint32_t m = size - 1u;
+    const uint32_t y0 = cy * 2654435761u, y1 = y0 + 2654435761u, z0 = cz * 805459861u, z1 = z0 + 805459861u;
+    const uint32_t x1 = cx + 1u;
+    L.idx[0] = (cx ^ y0 ^ z0) & m; L.idx[1] = (x1 ^ y0 ^ z0) & m; L.idx[2] = (cx ^ y1 ^ z0) & m; L.idx[3] = (x1 ^ y1 ^ z0) & m;
+    L.idx[4] = (cx ^ y0 ^ z1) & m; L.idx[5] = (x1 ^ y0 ^ z1) & m; L.idx[6] = (cx ^ y1 ^ z1) & m; L.idx[7] = (x1 ^ y1 ^ z1) & m;
+  } else {                                             // hashed, general size
+    const uint32_t y0 = cy * 2654435761u, y1 = y0 + 2654435761u, z0 = cz * 805459861u, z1 = z0 + 805459861u;
+    const uint32_t x1 = cx + 1u;
+    L.idx[0] = (cx ^ y0 ^ z0) % size; L.idx[1] = (x1 ^ y0 ^ z0) % size; L.idx[2] = (cx ^ y1 ^ z0) % size; L.idx[3] = (x1 ^ y1 ^ z0) % size;
+    L.idx[4] = (cx ^ y0 ^ z1) % size; L.idx[5] = (x1 ^ y0 ^ z1) % size; L.idx[6] = (cx ^ y1 ^ z1) % size; L.idx[7] = (x1 ^ y1 ^ z1) % size;
+  }
+  return L;
+}
+
+}  // namespace rnb
