@@ -556,7 +556,7 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
                             const float* dL_dsigmas, const float* dL_drgbs, float loss_scale, float* grad_table,
                             float* const* grad_geo, float* const* grad_rgb, rnb_stream_t stream);
 static int g_fwd_impl = 1;   // 1 = tcgen05 (field_tc.cu), 0 = mma.sync (this file)
-static int g_bwd_impl = 0;
+static int g_bwd_impl = 1;
 
 extern "C" {
 
@@ -595,6 +595,9 @@ int rnb_field_bwd(const rnb_field_params* P, const rnb_samples* S, const rnb_fie
   if (int rc = make_field_args(P, S, &A, what)) return rc;
   RNB_REQUIRE(saved && saved->enc && saved->rgb_in && saved->geo_h && saved->rgb_h1 && saved->rgb_h2 && saved->sraw, what);
   RNB_REQUIRE(rgb4_f16 && dL_dsigmas && dL_drgbs && grad_table && grad_geo && grad_rgb && loss_scale > 0.f, what);
+  for (int i = 0; i < P->K; i++) RNB_REQUIRE(grad_geo[i] && grad_rgb[i], what);
+  if (g_bwd_impl == 1)
+    return rnb_field_bwd_tc_launch(P, S, saved, rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, grad_geo, grad_rgb, stream);
   GradPtrs G;
   for (int i = 0; i < P->K; i++) { RNB_REQUIRE(grad_geo[i] && grad_rgb[i], what); G.geo[i] = grad_geo[i]; G.rgb[i] = grad_rgb[i]; }
   int n_agg = 0;

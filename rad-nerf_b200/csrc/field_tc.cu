@@ -268,6 +268,329 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
   if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
 }
 
+
+// ================================ backward on tcgen05 ================================================
+// One persistent CTA per SM: kWGB warpgroups (thread = sample, one 128-sample tile each) plus ONE
+// issuer warp whose elected lane issues every tcgen05.mma of the CTA, so that products accumulating
+// into shared TMEM columns are strictly ordered.  Per tile and layer l (rgb3, rgb2, rgb1, geo2, geo1):
+//   warpgroup:  writes its row of dZ_l into the `dz` operand tile and copies its row of the saved input
+//               In_l (global) into the `in` tile, fences, arrives on full[wg];
+//   issuer:     dW_l (TMEM, persists across all tiles of the pass, M = 64 out-neurons x N = in-features)
+//               += dZ_l^T In_l  -- eight K=16 steps over the tile's 128 samples, BOTH operands read as
+//               MN-major views of the very tiles the threads wrote row by row (tc05.cuh);
+//               dA (TMEM, per warpgroup) = dZ_l W_l -- W_l staged once per pass in its forward layout
+//               and read as an MN-major B operand; tcgen05.commit -> done[wg];
+//   warpgroup:  reads ITS row of dA from TMEM, applies relu'(In_l) with its own row of the `in` tile,
+//               and that is dZ_{l-1}.  After geo1 the row is d(encoding): the thread scatters it.
+// The weight gradients leave TMEM once per pass and CTA (64 x N fp32 each), not once per tile.
+constexpr int kWGB = 4;
+
+struct TcBwdSmem {
+  static constexpr int wend = TcSmem::wend;                       // same weight tiles as the forward kernel
+  static constexpr int wg0 = (wend + 127) / 128 * 128;
+  static constexpr int dz = 0;                                    // 128 x 64 fp16
+  static constexpr int in = kRows * 64 * 2;                       // 128 x 64 fp16
+  static constexpr int per_wg = 2 * kRows * 64 * 2;
+  static constexpr int bars = wg0 + kWGB * per_wg;                // full[kWGB], done[kWGB]
+  static constexpr int tmem_slot = bars + 2 * kWGB * 8;
+  static constexpr int bytes = tmem_slot + 16;
+};
+// TMEM columns: per-warpgroup dA accumulators, then the five persistent weight-gradient accumulators
+constexpr int kColD = 0, kColWg1 = 64 * kWGB, kColWg2 = kColWg1 + 32, kColWr1 = kColWg2 + 64, kColWr2 = kColWr1 + 32, kColWr3 = kColWr2 + 64;
+static_assert(kColWr3 + 64 <= 512, "TMEM budget");
+
+struct TcGradPtrs { float* geo[RNB_MAX_K]; float* rgb[RNB_MAX_K]; };
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(ok) : "r"(tc::smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+
+// dW (M = 64 rows of the dz tile's feature axis, N in-features) += dz^T in over the tile's 128 samples
+template <int N>
+__device__ __forceinline__ void tc_wgrad_mma(uint32_t d_tmem, uint32_t dz_s, uint32_t in_s, bool first) {
+  constexpr uint32_t idesc = tc::instr_desc(64, N, 1, 1);
+#pragma unroll
+  for (int k = 0; k < kRows / 16; k++)
+    tc::mma_f16(d_tmem, tc::smem_desc(dz_s + k * 256, 128, kRows * 16), tc::smem_desc(in_s + k * 256, 128, kRows * 16), idesc, !(first && k == 0));
+}
+// dA (128 x N) = dz (128 x KOUT, K-major) * W (KOUT out-rows x in-features tile, read MN-major from in-feature chunk c0)
+template <int N, int KOUT>
+__device__ __forceinline__ void tc_dgrad_mma(uint32_t d_tmem, uint32_t dz_s, uint32_t w_s, int c0) {
+  constexpr uint32_t idesc = tc::instr_desc(128, N, 0, 1);
+#pragma unroll
+  for (int k = 0; k < KOUT / 16; k++)
+    tc::mma_f16(d_tmem, tc::smem_desc(dz_s + k * 2 * (kRows * 16), kRows * 16, 128),
+                tc::smem_desc(w_s + c0 * (KOUT * 16) + k * 256, 128, KOUT * 16), idesc, k > 0);
+}
+
+// this thread's row of a saved activation (cap, W) -> W/8 chunks of the operand tile
+template <int W>
+__device__ __forceinline__ void tc_load_row(unsigned char* tile, int row, const __half* __restrict__ X, int64_t s, bool valid) {
+#pragma unroll
+  for (int c = 0; c < W / 8; c++) {
+    uint4 q = make_uint4(0u, 0u, 0u, 0u);
+    if (valid) q = __ldg(reinterpret_cast<const uint4*>(X + s * W) + c);
+    *reinterpret_cast<uint4*>(tile + tc::tile_chunk_off(kRows, row, c)) = q;
+  }
+}
+
+// dZ row = dA row (64 TMEM columns) masked by relu'(h) with h = this thread's row of the `in` tile
+__device__ __forceinline__ void tc_mask_row64(uint32_t taddr, const unsigned char* in_tile, unsigned char* dz_tile, int row) {
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    uint32_t r[32];
+    tc::tmem_ld32_nowait(taddr + h * 32, r);
+    tc::tmem_ld_wait();
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      const uint4 hv = *reinterpret_cast<const uint4*>(in_tile + tc::tile_chunk_off(kRows, row, h * 4 + c));
+      const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&hw[j]));
+        o[j] = pack2h(a.x > 0.f ? __uint_as_float(r[8 * c + 2 * j]) : 0.f, a.y > 0.f ? __uint_as_float(r[8 * c + 2 * j + 1]) : 0.f);
+      }
+      *reinterpret_cast<uint4*>(dz_tile + tc::tile_chunk_off(kRows, row, h * 4 + c)) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+__device__ __forceinline__ float tc_sat_h(float v) { return fminf(fmaxf(v, -65504.f), 65504.f); }
+
+// weight-gradient accumulator (M = 64: row i lives in TMEM lane 32*(i/16) + i%16) -> global fp32 gradient
+template <int N>
+__device__ __forceinline__ void tc_flush_wgrad(uint32_t tmem_cols, int n_out, float* __restrict__ gw, float inv_gs, int warp, int lane) {
+  const int o = (warp & 3) * 16 + lane;
+  const uint32_t taddr = tmem_cols + ((uint32_t)((warp & 3) * 32) << 16);
+#pragma unroll
+  for (int c0 = 0; c0 < N; c0 += 32) {
+    uint32_t r[32];
+    tc::tmem_ld32_nowait(taddr + c0, r);      // warp-collective: every lane executes it
+    tc::tmem_ld_wait();
+    if (lane < 16 && o < n_out) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        const float a = __uint_as_float(r[j]) * inv_gs, b = __uint_as_float(r[j + 1]) * inv_gs;
+        if (a != 0.f || b != 0.f) asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gw + o * N + c0 + j), "f"(a), "f"(b) : "memory");
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
+    TcFieldArgs A, const __half* __restrict__ s_enc, const __half* __restrict__ s_rgb_in, const __half* __restrict__ s_geo_h,
+    const __half* __restrict__ s_rgb_h1, const __half* __restrict__ s_rgb_h2, const __half* __restrict__ s_sraw,
+    const __half* __restrict__ rgb4, const float* __restrict__ dsig, const float* __restrict__ drgb, float gs,
+    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool is_issuer = warp == kWGB * 4;
+  const int wg = tid >> 7, row = tid & 127;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + TcBwdSmem::bars);
+  uint64_t* done = full + kWGB;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcBwdSmem::tmem_slot);
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
+  if (tid < kWGB) { tc::mbar_init(full + tid, 128); tc::mbar_init(done + tid, 1); }
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t w_s = tc::smem_u32(smem);
+  const float inv_gs = 1.0f / gs;
+  const int K = A.K;
+  uint32_t ph_full[kWGB] = {0, 0, 0, 0};   // issuer-side parities
+  uint32_t ph_done = 0;                    // warpgroup-side parity
+  for (int pass = 0; pass < K; pass++) {
+    const int64_t base = __ldg(A.seg + pass);
+    int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
+    if (pass_end > A.capacity) pass_end = A.capacity;
+    const int64_t n_tiles = pass_end > base ? (pass_end - base + kRows - 1) / kRows : 0;
+    // ---- stage this pass's weights (whole CTA) ----
+    __syncthreads();
+    {
+      const __half* gw = A.geo_w[pass];
+      const __half* rw = A.rgb_w[pass];
+      tc_stage_weight(smem + TcSmem::g1, gw, 64, 32, tid, kWGB * 128 + 32);
+      tc_stage_weight(smem + TcSmem::g2, gw + 64 * 32, 32, 64, tid, kWGB * 128 + 32);
+      tc_stage_weight(smem + TcSmem::r1, rw, 64, 32, tid, kWGB * 128 + 32);
+      tc_stage_weight(smem + TcSmem::r2, rw + 64 * 32, 64, 64, tid, kWGB * 128 + 32);
+      tc_stage_weight(smem + TcSmem::r3, rw + 64 * 32 + 64 * 64, 16, 64, tid, kWGB * 128 + 32);
+    }
+    tc::fence_async_smem();
+    __syncthreads();
+    const int64_t first_tile = (int64_t)blockIdx.x * kWGB;
+    const int64_t tile_stride = (int64_t)gridDim.x * kWGB;
+    if (is_issuer) {
+      // ---------------- issuer warp: every MMA of the CTA, in arrival order ----------------
+      if (lane == 0) {
+        int64_t left[kWGB]; int step[kWGB];
+        int remaining = 0;
+#pragma unroll
+        for (int g = 0; g < kWGB; g++) {
+          const int64_t t0 = first_tile + g;
+          left[g] = t0 < n_tiles ? (n_tiles - t0 + tile_stride - 1) / tile_stride : 0;
+          step[g] = 0;
+          remaining += (int)left[g];
+        }
+        bool first_w[5] = {true, true, true, true, true};
+        while (remaining > 0) {
+#pragma unroll
+          for (int g = 0; g < kWGB; g++) {
+            if (left[g] == 0) continue;
+            if (!mbar_test(full + g, ph_full[g])) continue;
+            ph_full[g] ^= 1;
+            tc::fence_after_sync();
+            const uint32_t dz_s = w_s + TcBwdSmem::wg0 + g * TcBwdSmem::per_wg + TcBwdSmem::dz;
+            const uint32_t in_s = dz_s + TcBwdSmem::in;
+            const uint32_t d_t = tmem + kColD + g * 64;
+            switch (step[g]) {
+              case 0:   // rgb layer 3: dZ (.,16), In = h2
+                tc_wgrad_mma<64>(tmem + kColWr3, dz_s, in_s, first_w[4]); first_w[4] = false;
+                tc_dgrad_mma<64, 16>(d_t, dz_s, w_s + TcSmem::r3, 0);
+                break;
+              case 1:   // rgb layer 2: dZ (.,64), In = h1
+                tc_wgrad_mma<64>(tmem + kColWr2, dz_s, in_s, first_w[3]); first_w[3] = false;
+                tc_dgrad_mma<64, 64>(d_t, dz_s, w_s + TcSmem::r2, 0);
+                break;
+              case 2:   // rgb layer 1: dZ (.,64), In = [SH | feature]; only d(feature) is needed (in-chunks 2,3)
+                tc_wgrad_mma<32>(tmem + kColWr1, dz_s, in_s, first_w[2]); first_w[2] = false;
+                tc_dgrad_mma<16, 64>(d_t, dz_s, w_s + TcSmem::r1, 2);
+                break;
+              case 3:   // geo layer 2: dZ (.,32), In = geo hidden
+                tc_wgrad_mma<64>(tmem + kColWg2, dz_s, in_s, first_w[1]); first_w[1] = false;
+                tc_dgrad_mma<64, 32>(d_t, dz_s, w_s + TcSmem::g2, 0);
+                break;
+              default:  // geo layer 1: dZ (.,64), In = encoding
+                tc_wgrad_mma<32>(tmem + kColWg1, dz_s, in_s, first_w[0]); first_w[0] = false;
+                tc_dgrad_mma<32, 64>(d_t, dz_s, w_s + TcSmem::g1, 0);
+                break;
+            }
+            tc::mma_commit(done + g);
+            if (++step[g] == 5) { step[g] = 0; left[g]--; remaining--; }
+          }
+        }
+      }
+      __syncwarp();
+    } else {
+      // ---------------- warpgroups: thread = sample ----------------
+      unsigned char* dzb = smem + TcBwdSmem::wg0 + wg * TcBwdSmem::per_wg + TcBwdSmem::dz;
+      unsigned char* inb = dzb + TcBwdSmem::in;
+      const uint32_t tmem_row = tmem + kColD + wg * 64 + ((uint32_t)((warp & 3) * 32) << 16);
+      for (int64_t tile = first_tile + wg; tile < n_tiles; tile += tile_stride) {
+        const int64_t s = base + tile * kRows + row;
+        const bool valid = s < pass_end;
+        // ---- step 0: rgb layer 3 (sigmoid): dZ = dL/drgb * gs * y (1 - y) ----
+        {
+          uint4 q = make_uint4(0u, 0u, 0u, 0u);
+          if (valid) {
+            const uint2 yq = __ldg(reinterpret_cast<const uint2*>(rgb4 + s * 4));
+            const float2 y01 = __half22float2(*reinterpret_cast<const __half2*>(&yq.x));
+            const float2 y23 = __half22float2(*reinterpret_cast<const __half2*>(&yq.y));
+            const float d0 = __ldg(drgb + 3 * s), d1 = __ldg(drgb + 3 * s + 1), d2 = __ldg(drgb + 3 * s + 2);
+            q.x = pack2h(tc_sat_h(d0 * gs * y01.x * (1.f - y01.x)), tc_sat_h(d1 * gs * y01.y * (1.f - y01.y)));
+            q.y = pack2h(tc_sat_h(d2 * gs * y23.x * (1.f - y23.x)), 0.f);
+          }
+          *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 0)) = q;
+          *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
+          tc_load_row<64>(inb, row, s_rgb_h2, s, valid);
+        }
+        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        // ---- step 1: rgb layer 2 ----
+        tc_mask_row64(tmem_row, inb, dzb, row);
+        tc_load_row<64>(inb, row, s_rgb_h1, s, valid);
+        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        // ---- step 2: rgb layer 1 ----
+        tc_mask_row64(tmem_row, inb, dzb, row);
+        tc_load_row<32>(inb, row, s_rgb_in, s, valid);
+        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        // ---- step 3: geo layer 2: dZ = [d raw sigma | d feature (16) | 0 ...] ----
+        {
+          float v[16];
+          tc::tmem_ld16(tmem_row, v);
+          float dsr = 0.f;
+          if (valid) {   // TruncExp backward: g * exp(clamp(x, -15, 15))  (custom_functions.py:170-173)
+            const float raw = __half2float(s_sraw[s]);
+            dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)));
+          }
+          uint4 q0, q1, q2;
+          q0.x = pack2h(dsr, v[0]); q0.y = pack2h(v[1], v[2]); q0.z = pack2h(v[3], v[4]); q0.w = pack2h(v[5], v[6]);
+          q1.x = pack2h(v[7], v[8]); q1.y = pack2h(v[9], v[10]); q1.z = pack2h(v[11], v[12]); q1.w = pack2h(v[13], v[14]);
+          q2.x = pack2h(v[15], 0.f); q2.y = 0u; q2.z = 0u; q2.w = 0u;
+          *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 0)) = q0;
+          *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = q1;
+          *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 2)) = q2;
+          *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 3)) = make_uint4(0u, 0u, 0u, 0u);
+          tc_load_row<64>(inb, row, s_geo_h, s, valid);
+        }
+        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        // ---- step 4: geo layer 1 ----
+        tc_mask_row64(tmem_row, inb, dzb, row);
+        tc_load_row<32>(inb, row, s_enc, s, valid);
+        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        // ---- step 5: d(encoding) row -> scatter into the fp32 table gradient ----
+        {
+          uint32_t r[32];
+          tc::tmem_ld32_nowait(tmem_row, r);
+          tc::tmem_ld_wait();
+          tc::fence_before_sync();
+          float x = 0.f, y = 0.f, z = 0.f;
+          if (valid) {
+            const int ry = __ldg(A.ray_id + s);
+            const float t = __ldg(A.ts + s);
+            x = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry), t, __ldg(A.rays_o + 3 * ry)) - A.xmin[0], A.xden[0]), 0.f), 1.f);
+            y = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 1), t, __ldg(A.rays_o + 3 * ry + 1)) - A.xmin[1], A.xden[1]), 0.f), 1.f);
+            z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 2), t, __ldg(A.rays_o + 3 * ry + 2)) - A.xmin[2], A.xden[2]), 0.f), 1.f);
+          }
+#pragma unroll
+          for (int l = 0; l < 16; l++) {
+            const uint32_t off = A.g.offset[l];
+            const LevelCorners L = level_corners(x, y, z, A.g.scale[l], A.g.res[l], A.g.offset[l + 1] - off);
+            // the activation gradient is carried in fp16 like the operator path: round, then un-scale
+            const float2 d = __half22float2(__floats2half2_rn(__uint_as_float(r[2 * l]), __uint_as_float(r[2 * l + 1])));
+            const float d0 = d.x * inv_gs, d1 = d.y * inv_gs;
+            float* gl = grad_table + 2 * (size_t)off;
+            const bool aggregate = l < n_aggregate_levels;   // warp-uniform
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+              if (aggregate) scatter_aggregated(gl, L.idx[k], L.w[k] * d0, L.w[k] * d1, valid);
+              else if (valid) red_add_f32x2(gl + 2 * (size_t)L.idx[k], L.w[k] * d0, L.w[k] * d1);
+            }
+          }
+        }
+      }
+    }
+    // ---- end of pass: weight gradients TMEM -> global (once per pass and CTA) ----
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    if (warp < 4 && first_tile < n_tiles) {
+      float* gg = G.geo[pass]; float* gr = G.rgb[pass];
+      tc_flush_wgrad<32>(tmem + kColWg1, 64, gg, inv_gs, warp, lane);
+      tc_flush_wgrad<64>(tmem + kColWg2, 32, gg + 64 * 32, inv_gs, warp, lane);
+      tc_flush_wgrad<32>(tmem + kColWr1, 64, gr, inv_gs, warp, lane);
+      tc_flush_wgrad<64>(tmem + kColWr2, 64, gr + 64 * 32, inv_gs, warp, lane);
+      tc_flush_wgrad<64>(tmem + kColWr3, 16, gr + 64 * 32 + 64 * 64, inv_gs, warp, lane);
+    }
+    tc::fence_before_sync();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
 }  // namespace rnb
 
 using namespace rnb;
@@ -300,5 +623,38 @@ int rnb_field_fwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   else
     field_fwd_tc_kernel<false><<<grid, kWG * 128, TcSmem::bytes, as_stream(stream)>>>(A, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, sigmas,
                                                                                      (__half*)rgb4_f16);
+  return check_launch(what);
+}
+
+int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, const void* rgb4_f16,
+                            const float* dL_dsigmas, const float* dL_drgbs, float loss_scale, float* grad_table,
+                            float* const* grad_geo, float* const* grad_rgb, rnb_stream_t stream) {
+  const char* what = "rnb_field_bwd(tcgen05)";
+  TcFieldArgs A;
+  RNB_REQUIRE(P != nullptr && S != nullptr && P->K >= 1 && P->K <= RNB_MAX_K && P->grid.n_levels == 16, what);
+  if (int rc = to_levels(&P->grid, &A.g, what)) return rc;
+  for (int c = 0; c < 3; c++) { A.xmin[c] = P->xyz_min[c]; A.xden[c] = P->xyz_max[c] - P->xyz_min[c]; }
+  A.table = (const __half2*)P->table_f16;
+  TcGradPtrs G;
+  for (int i = 0; i < P->K; i++) {
+    A.geo_w[i] = (const __half*)P->geo_w_f16[i]; A.rgb_w[i] = (const __half*)P->rgb_w_f16[i];
+    G.geo[i] = grad_geo[i]; G.rgb[i] = grad_rgb[i];
+  }
+  A.K = P->K;
+  A.rays_o = S->rays_o; A.rays_d = S->rays_d; A.ray_id = S->ray_id; A.ts = S->ts; A.seg = S->seg; A.capacity = S->capacity;
+  int n_agg = 0;
+  for (int l = 0; l < A.g.n_levels; l++)
+    if ((uint64_t)A.g.res[l] * A.g.res[l] * A.g.res[l] <= (uint64_t)(A.g.offset[l + 1] - A.g.offset[l]) && A.g.res[l] <= 64) n_agg = l + 1;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RNB_CUDA(cudaFuncSetAttribute(field_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcBwdSmem::bytes), what);
+    attr_set = true;
+  }
+  const int64_t tiles = S->capacity / kRows;
+  int grid = (int)((tiles + kWGB - 1) / kWGB);
+  if (grid > kNumSMs) grid = kNumSMs;
+  field_bwd_tc_kernel<<<grid, kWGB * 128 + 32, TcBwdSmem::bytes, as_stream(stream)>>>(
+      A, (const __half*)saved->enc, (const __half*)saved->rgb_in, (const __half*)saved->geo_h, (const __half*)saved->rgb_h1,
+      (const __half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg);
   return check_launch(what);
 }
