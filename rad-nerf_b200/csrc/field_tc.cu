@@ -16,6 +16,8 @@
 //     phases of their own tiles (gather is L2-latency bound, the layer chain is a dependent sequence).
 // Rounding points are those of the operator path (fp16 features / activations / outputs, fp32
 // accumulation), so this kernel, field.cu and radnerf_b200.tcnn agree to fp16 resolution.
+#include <stdlib.h>
+
 #include "hashgrid.cuh"
 #include "tc05.cuh"
 
@@ -340,6 +342,18 @@ __device__ __forceinline__ void tc_load_row(unsigned char* tile, int row, const 
   }
 }
 
+// split version of tc_load_row: issue the global loads early (before waiting for the previous MMA), park them later
+template <int W>
+__device__ __forceinline__ void tc_fetch_row(uint4 (&q)[8], const __half* __restrict__ X, int64_t s, bool valid) {
+#pragma unroll
+  for (int c = 0; c < W / 8; c++) q[c] = valid ? __ldg(reinterpret_cast<const uint4*>(X + s * W) + c) : make_uint4(0u, 0u, 0u, 0u);
+}
+template <int W>
+__device__ __forceinline__ void tc_store_row(unsigned char* tile, int row, const uint4 (&q)[8]) {
+#pragma unroll
+  for (int c = 0; c < W / 8; c++) *reinterpret_cast<uint4*>(tile + tc::tile_chunk_off(kRows, row, c)) = q[c];
+}
+
 // dZ row = dA row (64 TMEM columns) masked by relu'(h) with h = this thread's row of the `in` tile
 __device__ __forceinline__ void tc_mask_row64(uint32_t taddr, const unsigned char* in_tile, unsigned char* dz_tile, int row) {
 #pragma unroll
@@ -487,6 +501,8 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
       for (int64_t tile = first_tile + wg; tile < n_tiles; tile += tile_stride) {
         const int64_t s = base + tile * kRows + row;
         const bool valid = s < pass_end;
+        uint4 pre[8];
+        tc_fetch_row<64>(pre, s_rgb_h2, s, valid);
         // ---- step 0: rgb layer 3 (sigmoid): dZ = dL/drgb * gs * y (1 - y) ----
         {
           uint4 q = make_uint4(0u, 0u, 0u, 0u);
@@ -500,29 +516,32 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           }
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 0)) = q;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
-          tc_load_row<64>(inb, row, s_rgb_h2, s, valid);
+          tc_store_row<64>(inb, row, pre);
         }
         tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc_fetch_row<64>(pre, s_rgb_h1, s, valid);        // next layer's saved input: in flight while the MMAs run
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
         // ---- step 1: rgb layer 2 ----
         tc_mask_row64(tmem_row, inb, dzb, row);
-        tc_load_row<64>(inb, row, s_rgb_h1, s, valid);
+        tc_store_row<64>(inb, row, pre);
         tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc_fetch_row<32>(pre, s_rgb_in, s, valid);
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
         // ---- step 2: rgb layer 1 ----
         tc_mask_row64(tmem_row, inb, dzb, row);
-        tc_load_row<32>(inb, row, s_rgb_in, s, valid);
+        tc_store_row<32>(inb, row, pre);
         tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc_fetch_row<64>(pre, s_geo_h, s, valid);
+        float dsr = 0.f;
+        if (valid) {   // TruncExp backward: g * exp(clamp(x, -15, 15))  (custom_functions.py:170-173)
+          const float raw = __half2float(s_sraw[s]);
+          dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)));
+        }
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
         // ---- step 3: geo layer 2: dZ = [d raw sigma | d feature (16) | 0 ...] ----
         {
           float v[16];
           tc::tmem_ld16(tmem_row, v);
-          float dsr = 0.f;
-          if (valid) {   // TruncExp backward: g * exp(clamp(x, -15, 15))  (custom_functions.py:170-173)
-            const float raw = __half2float(s_sraw[s]);
-            dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)));
-          }
           uint4 q0, q1, q2;
           q0.x = pack2h(dsr, v[0]); q0.y = pack2h(v[1], v[2]); q0.z = pack2h(v[3], v[4]); q0.w = pack2h(v[5], v[6]);
           q1.x = pack2h(v[7], v[8]); q1.y = pack2h(v[9], v[10]); q1.z = pack2h(v[11], v[12]); q1.w = pack2h(v[13], v[14]);
@@ -531,14 +550,23 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = q1;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 2)) = q2;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 3)) = make_uint4(0u, 0u, 0u, 0u);
-          tc_load_row<64>(inb, row, s_geo_h, s, valid);
+          tc_store_row<64>(inb, row, pre);
         }
         tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc_fetch_row<32>(pre, s_enc, s, valid);
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
         // ---- step 4: geo layer 1 ----
         tc_mask_row64(tmem_row, inb, dzb, row);
-        tc_load_row<32>(inb, row, s_enc, s, valid);
+        tc_store_row<32>(inb, row, pre);
         tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        float x = 0.f, y = 0.f, z = 0.f;      // the sample's normalised position, for the scatter below
+        if (valid) {
+          const int ry = __ldg(A.ray_id + s);
+          const float t = __ldg(A.ts + s);
+          x = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry), t, __ldg(A.rays_o + 3 * ry)) - A.xmin[0], A.xden[0]), 0.f), 1.f);
+          y = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 1), t, __ldg(A.rays_o + 3 * ry + 1)) - A.xmin[1], A.xden[1]), 0.f), 1.f);
+          z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 2), t, __ldg(A.rays_o + 3 * ry + 2)) - A.xmin[2], A.xden[2]), 0.f), 1.f);
+        }
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
         // ---- step 5: d(encoding) row -> scatter into the fp32 table gradient ----
         {
@@ -546,27 +574,26 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           tc::tmem_ld32_nowait(tmem_row, r);
           tc::tmem_ld_wait();
           tc::fence_before_sync();
-          float x = 0.f, y = 0.f, z = 0.f;
-          if (valid) {
-            const int ry = __ldg(A.ray_id + s);
-            const float t = __ldg(A.ts + s);
-            x = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry), t, __ldg(A.rays_o + 3 * ry)) - A.xmin[0], A.xden[0]), 0.f), 1.f);
-            y = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 1), t, __ldg(A.rays_o + 3 * ry + 1)) - A.xmin[1], A.xden[1]), 0.f), 1.f);
-            z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 2), t, __ldg(A.rays_o + 3 * ry + 2)) - A.xmin[2], A.xden[2]), 0.f), 1.f);
-          }
+          // the activation gradient is carried in fp16 like the operator path: round, park the row in this
+          // thread's (now idle) dz row so that the level loop below stays rolled (small code, no I-cache misses)
 #pragma unroll
+          for (int c = 0; c < 4; c++)
+            *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, c)) =
+                make_uint4(pack2h(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])), pack2h(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3])),
+                           pack2h(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])), pack2h(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7])));
+#pragma unroll 1
           for (int l = 0; l < 16; l++) {
             const uint32_t off = A.g.offset[l];
             const LevelCorners L = level_corners(x, y, z, A.g.scale[l], A.g.res[l], A.g.offset[l + 1] - off);
-            // the activation gradient is carried in fp16 like the operator path: round, then un-scale
-            const float2 d = __half22float2(__floats2half2_rn(__uint_as_float(r[2 * l]), __uint_as_float(r[2 * l + 1])));
+            const float2 d = __half22float2(*reinterpret_cast<const __half2*>(dzb + tc::tile_chunk_off(kRows, row, l >> 2) + (l & 3) * 4));
             const float d0 = d.x * inv_gs, d1 = d.y * inv_gs;
             float* gl = grad_table + 2 * (size_t)off;
-            const bool aggregate = l < n_aggregate_levels;   // warp-uniform
+            if (l < n_aggregate_levels) {   // warp-uniform
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
-              if (aggregate) scatter_aggregated(gl, L.idx[k], L.w[k] * d0, L.w[k] * d1, valid);
-              else if (valid) red_add_f32x2(gl + 2 * (size_t)L.idx[k], L.w[k] * d0, L.w[k] * d1);
+              for (int k = 0; k < 8; k++) scatter_aggregated(gl, L.idx[k], L.w[k] * d0, L.w[k] * d1, valid);
+            } else if (valid) {
+#pragma unroll
+              for (int k = 0; k < 8; k++) red_add_f32x2(gl + 2 * (size_t)L.idx[k], L.w[k] * d0, L.w[k] * d1);
             }
           }
         }
@@ -645,6 +672,7 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   int n_agg = 0;
   for (int l = 0; l < A.g.n_levels; l++)
     if ((uint64_t)A.g.res[l] * A.g.res[l] * A.g.res[l] <= (uint64_t)(A.g.offset[l + 1] - A.g.offset[l]) && A.g.res[l] <= 64) n_agg = l + 1;
+  if (const char* e = getenv("RNB_AGG_LEVELS")) n_agg = atoi(e);   // tuning knob (profiles/): levels with warp-aggregated reductions
   static bool attr_set = false;
   if (!attr_set) {
     RNB_CUDA(cudaFuncSetAttribute(field_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcBwdSmem::bytes), what);
