@@ -669,9 +669,11 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   }
   A.K = P->K;
   A.rays_o = S->rays_o; A.rays_d = S->rays_d; A.ray_id = S->ray_id; A.ts = S->ts; A.seg = S->seg; A.capacity = S->capacity;
+  // levels whose cells are coarser than a few marching steps: runs of consecutive samples of a ray share corner
+  // entries there, so the warp combines them before issuing reductions (measured: profiles/r01_ab_agg_levels.txt)
   int n_agg = 0;
   for (int l = 0; l < A.g.n_levels; l++)
-    if ((uint64_t)A.g.res[l] * A.g.res[l] * A.g.res[l] <= (uint64_t)(A.g.offset[l + 1] - A.g.offset[l]) && A.g.res[l] <= 64) n_agg = l + 1;
+    if (A.g.res[l] <= 128) n_agg = l + 1;
   if (const char* e = getenv("RNB_AGG_LEVELS")) n_agg = atoi(e);   // tuning knob (profiles/): levels with warp-aggregated reductions
   static bool attr_set = false;
   if (!attr_set) {
