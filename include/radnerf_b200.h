@@ -319,6 +319,35 @@ int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float
                     int64_t n, float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                     rnb_stream_t stream);
 
+/* Ray_Gate.forward (networks.py:1087-1093): logits = MLP(cat(rays_o, rays_d) padded with ones to 16), softmax over
+ * the K logits in fp32, importance[k] = sum over rays.  gate_hidden_f16 ((4,n_rays,64), saved for the backward
+ * pass) may be NULL at inference.  Scratch buffers are the caller's: gate_in (n_rays,16) f16, gate_logits (n_rays,16) f16. */
+int rnb_gate_fwd(const void* gate_w_f16, const float* rays_o, const float* rays_d, int64_t n_rays, int K,
+                 void* gate_in_f16, void* gate_hidden_f16, void* gate_logits_f16, float* prob, float* importance,
+                 rnb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
+ * (test time) Full-frame rendering: replaces ml_render(test_time=True) = K x __render_rays_test
+ *     (ml_rendering.py:81-155; vren.raymarching_test binding.cpp:84-106, vren.composite_test_fw
+ *     binding.cpp:166-194) + background + gated blend (ml_rendering.py:64-77).  All K sub-NeRFs
+ *     advance together; one round = march (warp per alive ray, dense sample packing), fused field,
+ *     composite, and one 4K-byte read-back of the alive counts.  cfg: the engine config with
+ *     n_rays = rays of this call and sample_capacity >= K*n_rays*8 + 128*K.
+ * ------------------------------------------------------------------------------------ */
+typedef struct {
+  int64_t total_bytes;
+  int64_t gate_in, gate_logits, gate_prob, importance;
+  int64_t t_cur, t2, acc_opacity, acc_depth, acc_rgb, item_start, item_n, alive0, alive1, counters, seg;
+  int64_t ray_id, ts, sigmas, rgb4;
+} rnb_render_layout;
+int rnb_render_layout_of(const rnb_engine_config* cfg, rnb_render_layout* out);
+/* out: rgb (R,3), depth (R,K) ungated (Q19), opacity (R); pass_rgb (K,R,3) per-sub-NeRF colours after the
+ * background blend (may be NULL); stats_host[2] = {samples evaluated, rounds} (may be NULL).  bg_host (K,3).
+ * Synchronises the stream once per round (the reference: twice per round and sub-NeRF). */
+int rnb_render(const rnb_engine_config* cfg, void* workspace, const void* params_f16, const float* rays_o,
+               const float* rays_d, const uint8_t* const* bitfields, const float* bg_host, float* rgb, float* depth,
+               float* opacity, float* pass_rgb, int64_t* stats_host, rnb_stream_t stream);
+
 /* Optional per-stage device timing of the fused step (CUDA events around every stage; off by default).
  * Stage order: gate, march, scan, expand, field_fwd, composite_fw, blend_loss, composite_bw, field_bwd,
  * gate_bwd, adam.  rnb_engine_profile_read synchronises, returns the accumulated milliseconds and call

@@ -433,6 +433,20 @@ int rnb_engine_layout_of(const rnb_engine_config* c, rnb_engine_layout* L) {
 
 static const rnb_mlp_desc kGateDesc = {16, 16, 4, 0};
 
+int rnb_gate_fwd(const void* gate_w_f16, const float* rays_o, const float* rays_d, int64_t n_rays, int K, void* gate_in_f16,
+                 void* gate_hidden_f16, void* gate_logits_f16, float* prob, float* importance, rnb_stream_t stream) {
+  const char* what = "rnb_gate_fwd";
+  RNB_REQUIRE(gate_w_f16 && rays_o && rays_d && gate_in_f16 && gate_logits_f16 && prob && importance, what);
+  RNB_REQUIRE(n_rays >= 1 && K >= 2 && K <= RNB_MAX_K, what);
+  cudaStream_t st = as_stream(stream);
+  const int R = (int)n_rays;
+  eng_gate_in_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, (__half*)gate_in_f16);
+  if (int rc = rnb_mlp_fwd(&kGateDesc, gate_w_f16, gate_in_f16, R, gate_logits_f16, gate_hidden_f16, stream)) return rc;
+  RNB_CUDA(cudaMemsetAsync(importance, 0, K * 4, st), what);
+  eng_gate_softmax_kernel<<<ceil_div(R, 256), 256, 0, st>>>((const __half*)gate_logits_f16, R, K, prob, importance);
+  return check_launch(what);
+}
+
 int rnb_engine_gate(const rnb_engine_config* c, void* workspace, const void* params_f16, const float* rays_o,
                     const float* rays_d, rnb_stream_t stream) {
   const char* what = "rnb_engine_gate";
@@ -441,17 +455,9 @@ int rnb_engine_gate(const rnb_engine_config* c, void* workspace, const void* par
   rnb_engine_layout L;
   rnb_engine_layout_of(c, &L);
   char* ws = (char*)workspace;
-  cudaStream_t st = as_stream(stream);
-  const int R = c->n_rays;
-  StageTimer tm(ST_GATE, st);
-  __half* gate_in = (__half*)(ws + L.gate_in);
-  eng_gate_in_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, gate_in);
-  const __half* gw = (const __half*)params_f16 + c->gate_off;
-  if (int rc = rnb_mlp_fwd(&kGateDesc, gw, gate_in, R, ws + L.gate_logits, ws + L.gate_hidden, stream)) return rc;
-  RNB_CUDA(cudaMemsetAsync(ws + L.importance, 0, RNB_MAX_K * 4, st), what);
-  eng_gate_softmax_kernel<<<ceil_div(R, 256), 256, 0, st>>>((const __half*)(ws + L.gate_logits), R, c->K, (float*)(ws + L.gate_prob),
-                                                            (float*)(ws + L.importance));
-  return check_launch(what);
+  StageTimer tm(ST_GATE, as_stream(stream));
+  return rnb_gate_fwd((const __half*)params_f16 + c->gate_off, rays_o, rays_d, c->n_rays, c->K, ws + L.gate_in, ws + L.gate_hidden,
+                      ws + L.gate_logits, (float*)(ws + L.gate_prob), (float*)(ws + L.importance), stream);
 }
 
 int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32,

@@ -1,0 +1,292 @@
+// render.cu -- full-frame (test-time) rendering of all K sub-NeRFs with the gated blend.
+//
+// Replaces ml_render(test_time=True): K x __render_rays_test (models/ml_rendering.py:81-155) -- the
+// alive-ray loop around vren.raymarching_test / MNGP.forward / vren.composite_test_fw -- plus the
+// background and gate-weighted blend (ml_rendering.py:64-77).  The reference runs, per sub-NeRF and per
+// iteration, two vren kernels, ~10 ATen kernels (boolean-mask compaction and scatter), the tcnn kernels
+// and two host synchronisations, on zero-filled (N_alive, N_samples) slabs.  Here ALL K sub-NeRFs advance
+// together, one round = 4 launches and one 4*K-byte read-back:
+//   inf_march      warp per alive (pass, ray): resumes the chain at t_cur, takes up to NS samples
+//                  (march_warp.cuh), reserves a dense range of the pass's sample region with one atomicAdd
+//                  and writes (ray, t) -- no slabs, no masks, no memset;
+//   rnb_field_fwd  the fused tcgen05 field on the packed list (all passes, nothing saved);
+//   inf_composite  warp per alive (pass, ray): resumes T = 1 - opacity, composites its samples with the
+//                  reference's recurrence (volumerendering.cu:223-249), appends survivors to the next list.
+// NS follows the reference's schedule clamp(N_rays / N_alive, min, 64) (ml_rendering.py:115) with a floor of
+// 8 (Q13: the schedule only matters for the 1024-scheduled-samples cut-off).
+#include "aabb.cuh"
+#include "composite.cuh"
+#include "march_warp.cuh"
+
+namespace rnb {
+
+struct BitfieldPtrsR { const uint8_t* p[RNB_MAX_K]; };
+struct PassCounts { int32_t n[RNB_MAX_K]; int32_t base[RNB_MAX_K + 1]; };   // alive items / sample-region base per pass
+
+struct InfState {
+  float* t_cur; float* t2; float* opacity; float* depth; float* rgb;   // (K*R), rgb (K*R,3)
+  int32_t* item_start; int32_t* item_n;                                  // (K*R)
+  int32_t* alive[2];                                                     // (K*R) each, ping-pong
+  int32_t* alive_cnt[2];                                                 // (K) each
+  int32_t* sample_cnt;                                                   // (K) samples reserved in this round
+};
+
+// all (pass, ray) items alive; scene-box interval + NEAR_DISTANCE clamp (ml_rendering.py:48-50)
+__global__ void __launch_bounds__(256) inf_init_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, int R, int K,
+                                                       float cx, float cy, float cz, float hx, float hy, float hz, float near_d, InfState S) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  const float ox = rays_o[3 * r], oy = rays_o[3 * r + 1], oz = rays_o[3 * r + 2];
+  const float ix = __fdiv_rn(1.0f, rays_d[3 * r]), iy = __fdiv_rn(1.0f, rays_d[3 * r + 1]), iz = __fdiv_rn(1.0f, rays_d[3 * r + 2]);
+  const float2 hit = slab_test(ox, oy, oz, ix, iy, iz, cx, cy, cz, hx, hy, hz);
+  float t1 = -1.f, t2 = -1.f;
+  if (hit.y > 0) { t1 = fmaxf(hit.x, 0.0f); t2 = hit.y; }
+  if (t1 >= 0 && t1 < near_d) t1 = near_d;
+  for (int p = 0; p < K; p++) {
+    const int64_t i = (int64_t)p * R + r;
+    S.t_cur[i] = t1; S.t2[i] = t2; S.opacity[i] = 0.f; S.depth[i] = 0.f;
+    S.rgb[3 * i] = 0.f; S.rgb[3 * i + 1] = 0.f; S.rgb[3 * i + 2] = 0.f;
+    S.alive[0][i] = r;
+    if (r == 0) S.alive_cnt[0][p] = R;
+  }
+}
+
+__global__ void inf_round_begin_kernel(InfState S, int K, int out) {
+  if (threadIdx.x < K) { S.sample_cnt[threadIdx.x] = 0; S.alive_cnt[out][threadIdx.x] = 0; }
+}
+
+// flat alive-item index -> (pass, position in the pass's list)
+__device__ __forceinline__ bool locate_item(const PassCounts& C, int K, int64_t w, int& pass, int& j) {
+  int64_t acc = 0;
+  for (int p = 0; p < K; p++) {
+    if (w < acc + C.n[p]) { pass = p; j = (int)(w - acc); return true; }
+    acc += C.n[p];
+  }
+  return false;
+}
+
+template <bool kConstDt>
+__global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, MarchParams mp,
+                                                        BitfieldPtrsR bf, PassCounts C, int K, int R, int in, int NS, int64_t capacity,
+                                                        InfState S, int32_t* __restrict__ ray_id, float* __restrict__ ts) {
+  __shared__ float tbuf[8][64];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  int64_t total = 0;
+  for (int p = 0; p < K; p++) total += C.n[p];
+  for (int64_t w = (int64_t)blockIdx.x * 8 + wib; w < total; w += (int64_t)gridDim.x * 8) {
+    int pass, j;
+    locate_item(C, K, w, pass, j);
+    const int r = S.alive[in][(int64_t)pass * R + j];
+    const int64_t item = (int64_t)pass * R + r;
+    const Ray ray = load_ray(rays_o, rays_d, r);
+    const float t = S.t_cur[item], t2 = S.t2[item];
+    float t_next = t;
+    int n = 0;
+    if (t < t2) n = march_ray_warp<kConstDt>(ray, mp, bf.p[pass], t, t2, NS, tbuf[wib], t_next);   // raymarching.cu:365
+    __syncwarp();
+    int start = 0;
+    if (lane == 0 && n > 0) start = atomicAdd(S.sample_cnt + pass, n);
+    start = __shfl_sync(kFullMask, start, 0);
+    const int64_t o0 = (int64_t)C.base[pass] + start;
+    for (int k = lane; k < n; k += 32) {
+      if (o0 + k < capacity) { ray_id[o0 + k] = r; ts[o0 + k] = tbuf[wib][k]; }
+    }
+    if (lane == 0) {
+      S.item_start[item] = (int)o0; S.item_n[item] = n;
+      if (n > 0) S.t_cur[item] = t_next;            // only a taken sample moves the resume point (raymarching.cu:389-391)
+    }
+    __syncwarp();
+  }
+}
+
+// seg for rnb_field_fwd: pass bases (host-planned upper bounds) and the sample counts actually reserved
+__global__ void inf_seg_kernel(PassCounts C, int K, const int32_t* __restrict__ sample_cnt, int32_t* __restrict__ seg) {
+  const int p = threadIdx.x;
+  if (p < K) { seg[p] = C.base[p]; seg[K + 1 + p] = sample_cnt[p]; }
+  if (p == 0) seg[K] = C.base[K];
+}
+
+// Resume-able compositing of one round (volumerendering.cu:223-249), warp per alive item.
+__global__ void __launch_bounds__(256) inf_composite_kernel(const float* __restrict__ sigmas, const __half* __restrict__ rgb4,
+                                                            const float* __restrict__ ts, MarchParams mp, PassCounts C, int K, int R,
+                                                            int in, float T_threshold, int64_t capacity, InfState S) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  int64_t total = 0;
+  for (int p = 0; p < K; p++) total += C.n[p];
+  for (int64_t w = (int64_t)blockIdx.x * 8 + wib; w < total; w += (int64_t)gridDim.x * 8) {
+    int pass, j;
+    locate_item(C, K, w, pass, j);
+    const int r = S.alive[in][(int64_t)pass * R + j];
+    const int64_t item = (int64_t)pass * R + r;
+    int n = S.item_n[item];
+    const int64_t start = S.item_start[item];
+    if (start + n > capacity) n = start < capacity ? (int)(capacity - start) : 0;
+    if (n == 0) continue;                                   // no sample taken: the ray is finished (Q11)
+    float T = 1.0f - S.opacity[item];
+    float Rs = 0.f, Gs = 0.f, Bs = 0.f, Ds = 0.f, Os = 0.f;
+    bool dead = false;
+    for (int base = 0; base < n; base += 32) {
+      const int k = base + lane;
+      const bool valid = k < n;
+      float a = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, tt = 0.f;
+      if (valid) {
+        const int64_t s = start + k;
+        tt = ts[s];
+        a = 1.0f - __expf(-sigmas[s] * calc_dt(tt, mp));
+        load_rgb<true>(rgb4, s, cr, cg, cb);
+      }
+      const float om = 1.0f - a;
+      const float Tb = serial_T(om, T, lane);
+      const float Ta = __fmul_rn(Tb, om);
+      const unsigned term = __ballot_sync(kFullMask, valid && Ta <= T_threshold);
+      const int first = term ? (__ffs(term) - 1) : 32;
+      const float wgt = (valid && lane <= first) ? __fmul_rn(a, Tb) : 0.f;
+      Rs = fmaf(wgt, cr, Rs); Gs = fmaf(wgt, cg, Gs); Bs = fmaf(wgt, cb, Bs); Ds = fmaf(wgt, tt, Ds); Os += wgt;
+      if (term) { dead = true; break; }
+    }
+    Rs = warp_sum(Rs); Gs = warp_sum(Gs); Bs = warp_sum(Bs); Ds = warp_sum(Ds); Os = warp_sum(Os);
+    if (lane == 0) {
+      S.opacity[item] += Os; S.depth[item] += Ds;
+      S.rgb[3 * item] += Rs; S.rgb[3 * item + 1] += Gs; S.rgb[3 * item + 2] += Bs;
+      if (!dead) S.alive[in ^ 1][(int64_t)pass * R + atomicAdd(S.alive_cnt[in ^ 1] + pass, 1)] = r;
+    }
+  }
+}
+
+struct BgR { float c[RNB_MAX_K][3]; };
+
+// background per sub-NeRF + gate-weighted blend (ml_rendering.py:149-153, 64-68)
+__global__ void __launch_bounds__(256) inf_finish_kernel(InfState S, const float* __restrict__ prob, BgR bg, int R, int K,
+                                                         float* __restrict__ rgb, float* __restrict__ depth, float* __restrict__ opacity,
+                                                         float* __restrict__ pass_rgb) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  float c[3] = {0.f, 0.f, 0.f}, o = 0.f;
+  for (int p = 0; p < K; p++) {
+    const int64_t i = (int64_t)p * R + r;
+    const float g = K > 1 ? prob[(int64_t)r * K + p] : 1.f;
+    const float oi = S.opacity[i];
+    for (int k = 0; k < 3; k++) {
+      const float ci = S.rgb[3 * i + k] + bg.c[p][k] * (1.f - oi);
+      if (pass_rgb) pass_rgb[3 * i + k] = ci;
+      c[k] = fmaf(ci, g, c[k]);
+    }
+    o = fmaf(oi, g, o);
+    depth[(int64_t)r * K + p] = S.depth[i];
+  }
+  rgb[3 * r] = c[0]; rgb[3 * r + 1] = c[1]; rgb[3 * r + 2] = c[2];
+  opacity[r] = o;
+}
+
+}  // namespace rnb
+
+using namespace rnb;
+
+extern "C" {
+
+int rnb_render_layout_of(const rnb_engine_config* c, rnb_render_layout* L) {
+  const char* what = "rnb_render_layout_of";
+  RNB_REQUIRE(c && L && c->K >= 1 && c->K <= RNB_MAX_K && c->n_rays >= 1, what);
+  const int64_t R = c->n_rays, K = c->K, S = c->sample_capacity;
+  RNB_REQUIRE(S % 128 == 0 && S >= (K * R * 8 + 127) / 128 * 128 + 128 * K, what);   // room for the first round at NS = 8
+  int64_t off = 0;
+  auto take = [&](int64_t bytes) { const int64_t o = off; off = (off + bytes + 255) / 256 * 256; return o; };
+  L->gate_in = take(R * 16 * 2); L->gate_logits = take(R * 16 * 2); L->gate_prob = take(R * K * 4); L->importance = take(RNB_MAX_K * 4);
+  L->t_cur = take(K * R * 4); L->t2 = take(K * R * 4); L->acc_opacity = take(K * R * 4); L->acc_depth = take(K * R * 4);
+  L->acc_rgb = take(K * R * 12); L->item_start = take(K * R * 4); L->item_n = take(K * R * 4);
+  L->alive0 = take(K * R * 4); L->alive1 = take(K * R * 4); L->counters = take(4 * RNB_MAX_K * 4);
+  L->seg = take((2 * RNB_MAX_K + 4) * 4);
+  L->ray_id = take(S * 4); L->ts = take(S * 4); L->sigmas = take(S * 4); L->rgb4 = take(S * 8);
+  L->total_bytes = off;
+  return RNB_OK;
+}
+
+int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f16, const float* rays_o, const float* rays_d,
+               const uint8_t* const* bitfields, const float* bg_host, float* rgb, float* depth, float* opacity, float* pass_rgb,
+               int64_t* stats_host, rnb_stream_t stream) {
+  const char* what = "rnb_render";
+  rnb_render_layout L;
+  if (int rc = rnb_render_layout_of(c, &L)) return rc;
+  RNB_REQUIRE(workspace && params_f16 && rays_o && rays_d && bitfields && bg_host && rgb && depth && opacity, what);
+  char* ws = (char*)workspace;
+  cudaStream_t st = as_stream(stream);
+  const int R = c->n_rays, K = c->K;
+  const int64_t S = c->sample_capacity;
+  const __half* p16 = (const __half*)params_f16;
+  if (K > 1) {
+    if (int rc = rnb_gate_fwd(p16 + c->gate_off, rays_o, rays_d, R, K, ws + L.gate_in, nullptr, ws + L.gate_logits,
+                              (float*)(ws + L.gate_prob), (float*)(ws + L.importance), stream)) return rc;
+  }
+  InfState St;
+  St.t_cur = (float*)(ws + L.t_cur); St.t2 = (float*)(ws + L.t2); St.opacity = (float*)(ws + L.acc_opacity);
+  St.depth = (float*)(ws + L.acc_depth); St.rgb = (float*)(ws + L.acc_rgb);
+  St.item_start = (int32_t*)(ws + L.item_start); St.item_n = (int32_t*)(ws + L.item_n);
+  St.alive[0] = (int32_t*)(ws + L.alive0); St.alive[1] = (int32_t*)(ws + L.alive1);
+  int32_t* counters = (int32_t*)(ws + L.counters);
+  St.alive_cnt[0] = counters; St.alive_cnt[1] = counters + RNB_MAX_K; St.sample_cnt = counters + 2 * RNB_MAX_K;
+  int32_t* seg = (int32_t*)(ws + L.seg);
+  int32_t* ray_id = (int32_t*)(ws + L.ray_id); float* ts = (float*)(ws + L.ts);
+  float* sigmas = (float*)(ws + L.sigmas); __half* rgb4 = (__half*)(ws + L.rgb4);
+  // hazard Q1: the reference's test kernel hands `cascades` to calc_dt where `scale` is expected
+  const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, (float)c->cascades);
+  BitfieldPtrsR bf;
+  for (int i = 0; i < K; i++) { RNB_REQUIRE(bitfields[i] != nullptr, what); bf.p[i] = bitfields[i]; }
+  inf_init_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, K, c->center[0], c->center[1], c->center[2], c->half_size[0],
+                                                    c->half_size[1], c->half_size[2], c->near_distance, St);
+  rnb_field_params P;
+  P.K = K; P.grid = c->grid;
+  for (int k = 0; k < 3; k++) { P.xyz_min[k] = c->xyz_min[k]; P.xyz_max[k] = c->xyz_max[k]; }
+  P.table_f16 = p16 + c->table_off;
+  for (int i = 0; i < K; i++) { P.geo_w_f16[i] = p16 + c->geo_off[i]; P.rgb_w_f16[i] = p16 + c->rgb_off[i]; }
+  PassCounts C;
+  for (int p = 0; p < K; p++) C.n[p] = R;
+  const int min_samples = c->exp_step_factor == 0.0f ? 1 : 4;   // ml_rendering.py:108
+  int scheduled = 0, in = 0, rounds = 0;
+  int64_t total_samples = 0;
+  while (scheduled < c->max_samples) {
+    int64_t alive = 0;
+    for (int p = 0; p < K; p++) alive += C.n[p];
+    if (alive == 0) break;
+    // N_samples = max(min(N_rays // N_alive, 64), min_samples) (ml_rendering.py:115), floor 8, bounded by the workspace
+    int64_t NS = ((int64_t)K * R) / alive;
+    if (NS > 64) NS = 64;
+    if (NS < min_samples) NS = min_samples;
+    if (NS < 8) NS = 8;
+    while (NS > 1) {
+      int64_t need = 0;
+      for (int p = 0; p < K; p++) need += ((int64_t)C.n[p] * NS + 127) / 128 * 128;
+      if (need <= S) break;
+      NS--;
+    }
+    scheduled += (int)NS;
+    int64_t base = 0;
+    for (int p = 0; p < K; p++) { C.base[p] = (int32_t)base; base += ((int64_t)C.n[p] * NS + 127) / 128 * 128; }
+    C.base[K] = (int32_t)base;
+    inf_round_begin_kernel<<<1, 32, 0, st>>>(St, K, in ^ 1);
+    int grid = ceil_div(alive, 8);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    if (c->exp_step_factor == 0.0f)
+      inf_march_kernel<true><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts);
+    else
+      inf_march_kernel<false><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts);
+    inf_seg_kernel<<<1, 32, 0, st>>>(C, K, St.sample_cnt, seg);
+    if (int rc = check_launch(what)) return rc;
+    rnb_samples Sm = {rays_o, rays_d, ray_id, ts, seg, base > 0 ? base : 128};
+    if (int rc = rnb_field_fwd(&P, &Sm, nullptr, sigmas, rgb4, stream)) return rc;
+    inf_composite_kernel<<<grid, 256, 0, st>>>(sigmas, rgb4, ts, mp, C, K, R, in, c->T_threshold, S, St);
+    if (int rc = check_launch(what)) return rc;
+    int32_t host_cnt[2 * RNB_MAX_K + RNB_MAX_K];
+    RNB_CUDA(cudaMemcpyAsync(host_cnt, counters, sizeof(int32_t) * 3 * RNB_MAX_K, cudaMemcpyDeviceToHost, st), what);
+    RNB_CUDA(cudaStreamSynchronize(st), what);
+    in ^= 1;
+    for (int p = 0; p < K; p++) { C.n[p] = host_cnt[in * RNB_MAX_K + p]; total_samples += host_cnt[2 * RNB_MAX_K + p]; }
+    rounds++;
+  }
+  BgR bg;
+  for (int i = 0; i < K; i++) for (int k = 0; k < 3; k++) bg.c[i][k] = bg_host[3 * i + k];
+  inf_finish_kernel<<<ceil_div(R, 256), 256, 0, st>>>(St, (const float*)(ws + L.gate_prob), bg, R, K, rgb, depth, opacity, pass_rgb);
+  if (stats_host) { stats_host[0] = total_samples; stats_host[1] = rounds; }
+  return check_launch(what);
+}
+
+}  // extern "C"

@@ -45,6 +45,14 @@ class _Layout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int64) for n in _LAYOUT_FIELDS]
 
 
+_RENDER_LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_logits", "gate_prob", "importance", "t_cur", "t2", "acc_opacity", "acc_depth",
+                         "acc_rgb", "item_start", "item_n", "alive0", "alive1", "counters", "seg", "ray_id", "ts", "sigmas", "rgb4"]
+
+
+class _RenderLayout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int64) for n in _RENDER_LAYOUT_FIELDS]
+
+
 class Engine:
     def __init__(self, model, gate=None, n_rays=8192, exp_step_factor=0.0, samples_per_ray=128, max_samples=1024,
                  T_threshold=1e-4, near_distance=0.01, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
@@ -191,6 +199,56 @@ class Engine:
         if self.K > 1:
             out["gating_code"] = self.gate_prob
             out["gating_importance"] = self.importance
+        return out
+
+    # -- test-time rendering ----------------------------------------------------------------------------------
+    def _render_plan(self, n_rays, samples_per_ray):
+        key = (n_rays, samples_per_ray)
+        plan = getattr(self, "_render_cache", None)
+        if plan is None or plan[0] != key:
+            c = _Config()
+            ctypes.memmove(ctypes.byref(c), ctypes.byref(self.cfg), ctypes.sizeof(_Config))
+            c.n_rays = n_rays
+            c.sample_capacity = (n_rays * self.K * max(int(samples_per_ray), 8) + 127) // 128 * 128 + 128 * self.K
+            L = _RenderLayout()
+            call("rnb_render_layout_of", ctypes.byref(c), ctypes.byref(L))
+            ws = torch.empty(L.total_bytes, dtype=torch.uint8, device=self.device)
+            plan = (key, c, L, ws)
+            self._render_cache = plan
+        return plan[1:]
+
+    @torch.no_grad()
+    def render(self, rays_o, rays_d, chunk=1 << 19, samples_per_ray=16, with_pass_rgb=False):
+        """ml_render(test_time=True) (ml_rendering.py:18-77, 81-155) for a whole frame: all K sub-NeRFs advance
+        together through rnb_render, `chunk` rays per call.  Returns the reference's result dict (+ "total_samples")."""
+        _lib.check_input(rays_o, "rays_o", torch.float32)
+        _lib.check_input(rays_d, "rays_d", torch.float32)
+        self.sync_params()
+        N, K, dev = rays_o.shape[0], self.K, self.device
+        rgb = torch.empty(N, 3, device=dev); depth = torch.empty(N, K, device=dev); opacity = torch.empty(N, device=dev)
+        pass_rgb = torch.empty(K, N, 3, device=dev) if with_pass_rgb else None
+        gating = torch.empty(N, K, device=dev) if K > 1 else None
+        bfs = self.bitfields()
+        bf_arr = (ctypes.c_void_p * K)(*[b.data_ptr() for b in bfs])
+        bg_arr = (ctypes.c_float * (3 * K))(*[float(x) for row in self.background(False) for x in row])
+        stats = (ctypes.c_int64 * 2)()
+        total, rounds = 0, 0
+        for a in range(0, N, chunk):
+            n = min(chunk, N - a)
+            c, L, ws = self._render_plan(n, samples_per_ray)
+            tmp_pass = torch.empty(K, n, 3, device=dev) if with_pass_rgb else None
+            call("rnb_render", ctypes.byref(c), ws, self.flat16, rays_o[a:a + n], rays_d[a:a + n], bf_arr, bg_arr,
+                 rgb[a:a + n], depth[a:a + n], opacity[a:a + n], tmp_pass, stats, stream_arg(dev))
+            if with_pass_rgb:
+                pass_rgb[:, a:a + n] = tmp_pass
+            if K > 1:
+                gating[a:a + n] = ws[L.gate_prob:L.gate_prob + n * K * 4].view(torch.float32).view(n, K)
+            total += stats[0]; rounds += stats[1]
+        out = {"rgb": rgb, "depth": depth, "opacity": opacity, "total_samples": total, "rounds": rounds, "independent_rgbs": None}
+        if with_pass_rgb:
+            out["pass_rgb"] = pass_rgb
+        if K > 1:
+            out["gating_code"] = gating
         return out
 
     def sample_stats(self):

@@ -1,0 +1,63 @@
+"""Test-time frame rendering: the fused renderer (Engine.render -> rnb_render) next to the reference-shaped
+python loop (ml_render(test_time=True) over the vren/tcnn drop-ins) on one synthetic frame per workload.
+Prints one JSON line per workload; device time by CUDA events, 3 timed repetitions after 1 warm-up.
+Usage: python scripts/bench_render.py [workload ...]"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from bench import scene_bitfields, workload  # noqa: E402
+
+
+def timed(fn, reps):
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps, out
+
+
+def main():
+    names = sys.argv[1:] or ["ngp_blender_k1", "radnerf_tat_k2", "radnerf_tat_k8_infer"]
+    from radnerf_b200.trainer import Trainer
+    from radnerf_b200.models.ml_rendering import ml_render
+    from radnerf_b200.models.rendering import render
+    for name in names:
+        syn, w = workload(name)
+        tr = Trainer(scale=w["scale"], K=w["K"], freeze_occupancy=True, device="cuda:0", engine=True, batch_rays=8192)
+        tr.set_occupancy(scene_bitfields(syn, w))
+        cam = syn.make_cameras(100, w["radius"], w["H"], w["W"], w["fx"])
+        o, d = syn.full_image_rays(cam, 3)
+        o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        eng = tr.engine
+        eng.render(o, d)
+        ms, res = timed(lambda: eng.render(o, d), 3)
+        line = {"workload": name, "rays": int(o.shape[0]), "K": w["K"], "fused_ms": round(ms, 3),
+                "samples": int(res["total_samples"]), "rounds": int(res["rounds"]),
+                "Msamples_per_s": round(res["total_samples"] / ms / 1e3, 1)}
+        if os.environ.get("RNB_SKIP_PY") != "1":
+            esf = tr.exp_step_factor
+
+            def py():
+                with torch.no_grad():
+                    if w["K"] == 1:
+                        return render(tr.model, o, d, test_time=True, exp_step_factor=esf)
+                    return ml_render(tr.model, tr.gate, o, d, d, test_time=True, exp_step_factor=esf)
+            py()
+            ms_py, ref = timed(py, 1)
+            line["python_surface_ms"] = round(ms_py, 3)
+            line["max_abs_rgb_diff"] = float((ref["rgb"].float() - res["rgb"]).abs().max())
+        print(json.dumps(line), flush=True)
+        del tr, eng
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()
