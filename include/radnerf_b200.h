@@ -226,8 +226,10 @@ typedef struct {
   int64_t capacity;                    /* multiple of 128                                            */
 } rnb_samples;
 
-/* Activations saved by the forward pass for the backward pass (all (capacity, W) row-major f16).
- * Any pointer may be NULL in inference (then nothing is saved). */
+/* Activations saved by the forward pass for the backward pass: capacity*W f16 each, OPAQUE between
+ * rnb_field_fwd and rnb_field_bwd.  (Default tcgen05 implementation: per 128-sample tile the shared-memory
+ * operand image [W/8][128][8], written and read back with one bulk copy per tile and layer; element (s, f)
+ * of a tile is at half-index (f/8)*1024 + s*8 + f%8.)  Pass saved = NULL in inference (nothing is saved). */
 typedef struct {
   void* enc;      /* (cap,32) hash-grid features                                   */
   void* rgb_in;   /* (cap,32) [SH4(16) | geometry feature(16)]                     */
@@ -358,7 +360,7 @@ int rnb_engine_profile_read(double* ms, int32_t* calls, int n);
 /* Selects the implementation behind rnb_field_fwd / rnb_field_bwd: 1 = tcgen05 + TMEM kernels
  * (csrc/field_tc.cu, default where available), 0 = mma.sync register-chained kernels (csrc/field.cu).
  * Both compute the same operator; the switch exists for A/B measurement and parity tests. */
-int rnb_set_field_impl(int fwd_tcgen05, int bwd_tcgen05);
+int rnb_set_field_impl(int fwd_tcgen05, int bwd_tcgen05);   /* both or neither: the saved layouts differ */
 
 /* Diagnostics: self-test of the tcgen05 building blocks (csrc/tc05.cuh) on one CTA.
  * X (128,64), W (64,64), Y (128,32) f16 row-major -> out1 (128,64) = X W^T, out2 (128,32) = raw TMEM

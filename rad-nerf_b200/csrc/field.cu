@@ -561,6 +561,8 @@ static int g_bwd_impl = 1;
 extern "C" {
 
 int rnb_set_field_impl(int fwd_tcgen05, int bwd_tcgen05) {
+  // the two implementations keep the saved activations in different layouts (operand tiles vs rows): no mixing
+  RNB_REQUIRE((fwd_tcgen05 != 0) == (bwd_tcgen05 != 0), "rnb_set_field_impl");
   g_fwd_impl = fwd_tcgen05 ? 1 : 0;
   g_bwd_impl = bwd_tcgen05 ? 1 : 0;
   return RNB_OK;

@@ -99,8 +99,8 @@ __device__ __forceinline__ void tc_layer_mma(uint32_t d_tmem, uint32_t a_smem, u
 // named barrier over the 128 threads of a warpgroup (barrier ids 1..kWG; 0 is __syncthreads)
 __device__ __forceinline__ void wg_sync(int wg) { asm volatile("bar.sync %0, 128;" ::"r"(wg + 1) : "memory"); }
 
-// 64 accumulator columns of this thread's row -> ReLU -> fp16 -> 8 operand chunks (+ optional global row)
-__device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* tile, int row, __half* __restrict__ save_row) {
+// 64 accumulator columns of this thread's row -> ReLU -> fp16 -> 8 operand chunks
+__device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* tile, int row) {
 #pragma unroll
   for (int h = 0; h < 2; h++) {
     uint32_t r[32];
@@ -114,8 +114,24 @@ __device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* til
       q.z = pack2h(fmaxf(__uint_as_float(r[8 * c + 4]), 0.f), fmaxf(__uint_as_float(r[8 * c + 5]), 0.f));
       q.w = pack2h(fmaxf(__uint_as_float(r[8 * c + 6]), 0.f), fmaxf(__uint_as_float(r[8 * c + 7]), 0.f));
       *reinterpret_cast<uint4*>(tile + tc::tile_chunk_off(kRows, row, h * 4 + c)) = q;
-      if (save_row) reinterpret_cast<uint4*>(save_row)[h * 4 + c] = q;
     }
+  }
+}
+
+// One layer step of the forward chain, executed by the warpgroup's elected thread: issue the layer's MMAs and, when
+// activations are saved for the backward pass, copy the operand tile the MMAs read -- it already has the layout the
+// backward kernel wants -- to global memory with one bulk store.  The warpgroup's mbarrier completes when the MMAs
+// are done AND the store has finished reading the tile (2 arrivals), after which the tile may be overwritten.
+template <bool kSave, int N, int KDIM>
+__device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint32_t a_smem, uint32_t w_smem, __half* save_tile) {
+  tc::fence_after_sync();
+  tc_layer_mma<N, KDIM>(tmem_d, a_smem, w_smem);
+  tc::mma_commit(bar);
+  if (kSave) {
+    tc::bulk_store(save_tile, a_smem, kRows * KDIM * 2);
+    tc::bulk_commit();
+    tc::bulk_wait_read();
+    tc::mbar_arrive(bar);
   }
 }
 
@@ -129,7 +145,8 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcSmem::tmem_slot);
   if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
-  if (tid < kWG) tc::mbar_init(bars + tid, 1);
+  if (tid < kWG) tc::mbar_init(bars + tid, kSave ? 2 : 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -178,7 +195,6 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
           q.x = tc_encode_level(A, 4 * c, x, y, z); q.y = tc_encode_level(A, 4 * c + 1, x, y, z);
           q.z = tc_encode_level(A, 4 * c + 2, x, y, z); q.w = tc_encode_level(A, 4 * c + 3, x, y, z);
           *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, c)) = q;
-          if (kSave) reinterpret_cast<uint4*>(s_enc + s * 32)[c] = q;
         }
         // direction: d/|d| -> (d+1)/2 -> (tcnn) 2u-1 -> SH4   (networks.py:322-323)
         const float nrm = sqrtf(dx * dx + dy * dy + dz * dz);
@@ -195,15 +211,15 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<64, 32>(tmem_d, a8_s, w_s + TcSmem::g1); tc::mma_commit(bar); }
+      if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::g1, s_enc + s * 32);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
-      tc_relu_row64(tmem_row, b16, row, (kSave && valid) ? s_geo_h + s * 64 : nullptr);
+      tc_relu_row64(tmem_row, b16, row);
       // ---- geo layer 2: 64 -> 32 (col 0 = raw sigma, cols 1..16 = geometry feature) ----
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<32, 64>(tmem_d, b16_s, w_s + TcSmem::g2); tc::mma_commit(bar); }
+      if (row == 0) tc_fwd_step<kSave, 32, 64>(bar, tmem_d, b16_s, w_s + TcSmem::g2, s_geo_h + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       {
@@ -223,34 +239,30 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
         *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, 3)) = f1;
         if (valid) {
           sigmas[s] = expf(__half2float(raw));
-          if (kSave) {
-            s_sraw[s] = raw;
-            uint4* dst = reinterpret_cast<uint4*>(s_rgb_in + s * 32);
-            dst[0] = shq0; dst[1] = shq1; dst[2] = f0; dst[3] = f1;
-          }
+          if (kSave) s_sraw[s] = raw;
         }
       }
       // ---- rgb layer 1: 32 -> 64, ReLU ----
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<64, 32>(tmem_d, a8_s, w_s + TcSmem::r1); tc::mma_commit(bar); }
+      if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::r1, s_rgb_in + s * 32);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
-      tc_relu_row64(tmem_row, b16, row, (kSave && valid) ? s_rgb_h1 + s * 64 : nullptr);
+      tc_relu_row64(tmem_row, b16, row);
       // ---- rgb layer 2: 64 -> 64, ReLU ----
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<64, 64>(tmem_d, b16_s, w_s + TcSmem::r2); tc::mma_commit(bar); }
+      if (row == 0) tc_fwd_step<kSave, 64, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r2, s_rgb_h1 + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
-      tc_relu_row64(tmem_row, b16, row, (kSave && valid) ? s_rgb_h2 + s * 64 : nullptr);
+      tc_relu_row64(tmem_row, b16, row);
       // ---- rgb layer 3: 64 -> 16, sigmoid ----
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) { tc::fence_after_sync(); tc_layer_mma<16, 64>(tmem_d, b16_s, w_s + TcSmem::r3); tc::mma_commit(bar); }
+      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       {
@@ -265,6 +277,7 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
       tc::fence_before_sync();   // the next tile's first MMA overwrites the accumulator columns just read
     }
   }
+  if (kSave && row == 0) tc::bulk_wait_all();
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
@@ -291,10 +304,11 @@ struct TcBwdSmem {
   static constexpr int wend = TcSmem::wend;                       // same weight tiles as the forward kernel
   static constexpr int wg0 = (wend + 127) / 128 * 128;
   static constexpr int dz = 0;                                    // 128 x 64 fp16
-  static constexpr int in = kRows * 64 * 2;                       // 128 x 64 fp16
-  static constexpr int per_wg = 2 * kRows * 64 * 2;
-  static constexpr int bars = wg0 + kWGB * per_wg;                // full[kWGB], done[kWGB]
-  static constexpr int tmem_slot = bars + 2 * kWGB * 8;
+  static constexpr int in = kRows * 64 * 2;                       // 2 x (128 x 64 fp16): saved-input tiles, double-buffered
+  static constexpr int in_bytes = kRows * 64 * 2;
+  static constexpr int per_wg = 3 * kRows * 64 * 2;
+  static constexpr int bars = wg0 + kWGB * per_wg;                // full[kWGB], done[kWGB], loaded[kWGB][2]
+  static constexpr int tmem_slot = bars + 4 * kWGB * 8;
   static constexpr int bytes = tmem_slot + 16;
 };
 // TMEM columns: per-warpgroup dA accumulators, then the five persistent weight-gradient accumulators
@@ -303,9 +317,6 @@ static_assert(kColWr3 + 64 <= 512, "TMEM budget");
 
 struct TcGradPtrs { float* geo[RNB_MAX_K]; float* rgb[RNB_MAX_K]; };
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
-}
 __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
@@ -331,46 +342,37 @@ __device__ __forceinline__ void tc_dgrad_mma(uint32_t d_tmem, uint32_t dz_s, uin
                 tc::smem_desc(w_s + c0 * (KOUT * 16) + k * 256, 128, KOUT * 16), idesc, k > 0);
 }
 
-// this thread's row of a saved activation (cap, W) -> W/8 chunks of the operand tile
-template <int W>
-__device__ __forceinline__ void tc_load_row(unsigned char* tile, int row, const __half* __restrict__ X, int64_t s, bool valid) {
+// relu'(h) of this thread's row of a saved 64-wide hidden activation tile, as 64 bits
+__device__ __forceinline__ uint2 tc_row_mask64(const unsigned char* in_tile, int row) {
+  uint32_t m[2] = {0u, 0u};
 #pragma unroll
-  for (int c = 0; c < W / 8; c++) {
-    uint4 q = make_uint4(0u, 0u, 0u, 0u);
-    if (valid) q = __ldg(reinterpret_cast<const uint4*>(X + s * W) + c);
-    *reinterpret_cast<uint4*>(tile + tc::tile_chunk_off(kRows, row, c)) = q;
+  for (int c = 0; c < 8; c++) {
+    const uint4 hv = *reinterpret_cast<const uint4*>(in_tile + tc::tile_chunk_off(kRows, row, c));
+    const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+    for (int j = 0; j < 4; j++) {   // post-ReLU values are >= 0: positive <=> any magnitude bit set
+      m[c >> 2] |= ((hw[j] & 0x7FFFu) ? 1u : 0u) << ((c & 3) * 8 + 2 * j);
+      m[c >> 2] |= ((hw[j] & 0x7FFF0000u) ? 1u : 0u) << ((c & 3) * 8 + 2 * j + 1);
+    }
   }
+  return make_uint2(m[0], m[1]);
 }
 
-// split version of tc_load_row: issue the global loads early (before waiting for the previous MMA), park them later
-template <int W>
-__device__ __forceinline__ void tc_fetch_row(uint4 (&q)[8], const __half* __restrict__ X, int64_t s, bool valid) {
-#pragma unroll
-  for (int c = 0; c < W / 8; c++) q[c] = valid ? __ldg(reinterpret_cast<const uint4*>(X + s * W) + c) : make_uint4(0u, 0u, 0u, 0u);
-}
-template <int W>
-__device__ __forceinline__ void tc_store_row(unsigned char* tile, int row, const uint4 (&q)[8]) {
-#pragma unroll
-  for (int c = 0; c < W / 8; c++) *reinterpret_cast<uint4*>(tile + tc::tile_chunk_off(kRows, row, c)) = q[c];
-}
-
-// dZ row = dA row (64 TMEM columns) masked by relu'(h) with h = this thread's row of the `in` tile
-__device__ __forceinline__ void tc_mask_row64(uint32_t taddr, const unsigned char* in_tile, unsigned char* dz_tile, int row) {
+// dZ row = dA row (64 TMEM columns) masked by relu'(h) (bit f of `mask`)
+__device__ __forceinline__ void tc_mask_row64(uint32_t taddr, uint2 mask, unsigned char* dz_tile, int row) {
 #pragma unroll
   for (int h = 0; h < 2; h++) {
     uint32_t r[32];
     tc::tmem_ld32_nowait(taddr + h * 32, r);
     tc::tmem_ld_wait();
+    const uint32_t m = h ? mask.y : mask.x;
 #pragma unroll
     for (int c = 0; c < 4; c++) {
-      const uint4 hv = *reinterpret_cast<const uint4*>(in_tile + tc::tile_chunk_off(kRows, row, h * 4 + c));
-      const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
       uint32_t o[4];
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&hw[j]));
-        o[j] = pack2h(a.x > 0.f ? __uint_as_float(r[8 * c + 2 * j]) : 0.f, a.y > 0.f ? __uint_as_float(r[8 * c + 2 * j + 1]) : 0.f);
-      }
+      for (int j = 0; j < 4; j++)
+        o[j] = pack2h((m >> (8 * c + 2 * j)) & 1u ? __uint_as_float(r[8 * c + 2 * j]) : 0.f,
+                      (m >> (8 * c + 2 * j + 1)) & 1u ? __uint_as_float(r[8 * c + 2 * j + 1]) : 0.f);
       *reinterpret_cast<uint4*>(dz_tile + tc::tile_chunk_off(kRows, row, h * 4 + c)) = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
@@ -409,9 +411,13 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
   const int wg = tid >> 7, row = tid & 127;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + TcBwdSmem::bars);
   uint64_t* done = full + kWGB;
+  uint64_t* loaded = done + kWGB;          // [kWGB][2]: a saved-input tile has landed in buffer b of warpgroup g
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcBwdSmem::tmem_slot);
   if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
-  if (tid < kWGB) { tc::mbar_init(full + tid, 128); tc::mbar_init(done + tid, 1); }
+  if (tid < kWGB) {
+    tc::mbar_init(full + tid, 128); tc::mbar_init(done + tid, 1);
+    tc::mbar_init(loaded + 2 * tid, 1); tc::mbar_init(loaded + 2 * tid + 1, 1);
+  }
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   tc::fence_before_sync();
   __syncthreads();
@@ -421,7 +427,9 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
   const float inv_gs = 1.0f / gs;
   const int K = A.K;
   uint32_t ph_full[kWGB] = {0, 0, 0, 0};   // issuer-side parities
+  uint32_t in_buf[kWGB] = {0, 0, 0, 0};    // issuer-side: which saved-input buffer the next step of warpgroup g reads
   uint32_t ph_done = 0;                    // warpgroup-side parity
+  uint32_t q_load = 0;                     // warpgroup-side: saved-input tiles consumed so far (buffer = q & 1, parity = (q >> 1) & 1)
   for (int pass = 0; pass < K; pass++) {
     const int64_t base = __ldg(A.seg + pass);
     int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
@@ -463,7 +471,8 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
             ph_full[g] ^= 1;
             tc::fence_after_sync();
             const uint32_t dz_s = w_s + TcBwdSmem::wg0 + g * TcBwdSmem::per_wg + TcBwdSmem::dz;
-            const uint32_t in_s = dz_s + TcBwdSmem::in;
+            const uint32_t in_s = dz_s + TcBwdSmem::in + in_buf[g] * TcBwdSmem::in_bytes;
+            in_buf[g] ^= 1;
             const uint32_t d_t = tmem + kColD + g * 64;
             switch (step[g]) {
               case 0:   // rgb layer 3: dZ (.,16), In = h2
@@ -497,12 +506,33 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
       // ---------------- warpgroups: thread = sample ----------------
       unsigned char* dzb = smem + TcBwdSmem::wg0 + wg * TcBwdSmem::per_wg + TcBwdSmem::dz;
       unsigned char* inb = dzb + TcBwdSmem::in;
+      const uint32_t inb_s = tc::smem_u32(inb);
+      uint64_t* ld = loaded + 2 * wg;
       const uint32_t tmem_row = tmem + kColD + wg * 64 + ((uint32_t)((warp & 3) * 32) << 16);
-      for (int64_t tile = first_tile + wg; tile < n_tiles; tile += tile_stride) {
-        const int64_t s = base + tile * kRows + row;
+      const int64_t t0 = first_tile + wg;
+      const int64_t my_tiles = t0 < n_tiles ? (n_tiles - t0 + tile_stride - 1) / tile_stride : 0;
+      // Saved-input tiles arrive by bulk copy in the order the layers consume them: per tile h2, h1, rgb_in, geo_h, enc.
+      // The forward kernel stored them in the operand-tile layout, so they are MMA operands as they land.  Load number
+      // q (counted over the whole kernel) goes to buffer q & 1; it may be issued once the MMAs of load q - 2 are done.
+      auto issue_load = [&](int64_t n, int j, uint32_t q) {     // elected thread only
+        if (n >= my_tiles) return;
+        const int64_t s0 = base + (t0 + n * tile_stride) * kRows;
+        const __half* src = j == 0 ? s_rgb_h2 + s0 * 64 : j == 1 ? s_rgb_h1 + s0 * 64 : j == 2 ? s_rgb_in + s0 * 32 : j == 3 ? s_geo_h + s0 * 64
+                                                                                                                            : s_enc + s0 * 32;
+        const uint32_t bytes = (j == 2 || j == 4) ? kRows * 32 * 2 : kRows * 64 * 2;
+        tc::mbar_expect_tx(ld + (q & 1), bytes);
+        tc::bulk_load(inb_s + (q & 1) * TcBwdSmem::in_bytes, src, bytes, ld + (q & 1));
+      };
+      auto wait_load = [&]() -> const unsigned char* {          // every thread: the tile of load q_load is in shared memory
+        const unsigned char* p = inb + (q_load & 1) * TcBwdSmem::in_bytes;
+        tc::mbar_wait(ld + (q_load & 1), (q_load >> 1) & 1);
+        q_load++;
+        return p;
+      };
+      if (row == 0) { issue_load(0, 0, q_load); issue_load(0, 1, q_load + 1); }
+      for (int64_t n = 0; n < my_tiles; n++) {
+        const int64_t s = base + (t0 + n * tile_stride) * kRows + row;
         const bool valid = s < pass_end;
-        uint4 pre[8];
-        tc_fetch_row<64>(pre, s_rgb_h2, s, valid);
         // ---- step 0: rgb layer 3 (sigmoid): dZ = dL/drgb * gs * y (1 - y) ----
         {
           uint4 q = make_uint4(0u, 0u, 0u, 0u);
@@ -516,28 +546,28 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           }
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 0)) = q;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
-          tc_store_row<64>(inb, row, pre);
         }
-        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
-        tc_fetch_row<64>(pre, s_rgb_h1, s, valid);        // next layer's saved input: in flight while the MMAs run
+        uint2 mask = tc_row_mask64(wait_load(), row);                                     // relu'(h2)
+        tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        if (row == 0) issue_load(n, 2, q_load + 1);
         // ---- step 1: rgb layer 2 ----
-        tc_mask_row64(tmem_row, inb, dzb, row);
-        tc_store_row<64>(inb, row, pre);
-        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
-        tc_fetch_row<32>(pre, s_rgb_in, s, valid);
+        tc_mask_row64(tmem_row, mask, dzb, row);
+        mask = tc_row_mask64(wait_load(), row);                                           // relu'(h1)
+        tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        if (row == 0) issue_load(n, 3, q_load + 1);
         // ---- step 2: rgb layer 1 ----
-        tc_mask_row64(tmem_row, inb, dzb, row);
-        tc_store_row<32>(inb, row, pre);
-        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
-        tc_fetch_row<64>(pre, s_geo_h, s, valid);
+        tc_mask_row64(tmem_row, mask, dzb, row);
+        wait_load();                                                                      // [SH | feature]: no activation in front
+        tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
         float dsr = 0.f;
         if (valid) {   // TruncExp backward: g * exp(clamp(x, -15, 15))  (custom_functions.py:170-173)
           const float raw = __half2float(s_sraw[s]);
           dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)));
         }
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        if (row == 0) issue_load(n, 4, q_load + 1);
         // ---- step 3: geo layer 2: dZ = [d raw sigma | d feature (16) | 0 ...] ----
         {
           float v[16];
@@ -550,15 +580,15 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = q1;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 2)) = q2;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 3)) = make_uint4(0u, 0u, 0u, 0u);
-          tc_store_row<64>(inb, row, pre);
         }
-        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
-        tc_fetch_row<32>(pre, s_enc, s, valid);
+        mask = tc_row_mask64(wait_load(), row);                                           // relu'(geo hidden)
+        tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        if (row == 0) issue_load(n + 1, 0, q_load + 1);                                   // next tile's first input
         // ---- step 4: geo layer 1 ----
-        tc_mask_row64(tmem_row, inb, dzb, row);
-        tc_store_row<32>(inb, row, pre);
-        tc::fence_async_smem(); tc::fence_before_sync(); mbar_arrive(full + wg);
+        tc_mask_row64(tmem_row, mask, dzb, row);
+        wait_load();                                                                      // encoding
+        tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
         float x = 0.f, y = 0.f, z = 0.f;      // the sample's normalised position, for the scatter below
         if (valid) {
           const int ry = __ldg(A.ray_id + s);
@@ -568,6 +598,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 2), t, __ldg(A.rays_o + 3 * ry + 2)) - A.xmin[2], A.xden[2]), 0.f), 1.f);
         }
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        if (row == 0) issue_load(n + 1, 1, q_load + 1);
         // ---- step 5: d(encoding) row -> scatter into the fp32 table gradient ----
         {
           uint32_t r[32];

@@ -79,6 +79,13 @@ class Saved:
         self.c = _Saved(self.enc.data_ptr(), self.rgb_in.data_ptr(), self.geo_h.data_ptr(), self.rgb_h1.data_ptr(),
                         self.rgb_h2.data_ptr(), self.sraw.data_ptr())
 
+    def rows(self, name):
+        """A saved activation as (capacity, W) rows.  The kernels keep it as per-128-sample operand tiles
+        [W/8][128][8] (include/radnerf_b200.h, rnb_field_saved); this un-permutes a copy for inspection."""
+        t = getattr(self, name)
+        cap, W = t.shape
+        return t.view(cap // 128, W // 8, 128, 8).permute(0, 2, 1, 3).reshape(cap, W)
+
 
 def field_fwd(P, S, saved, sigmas, rgb4):
     call("rnb_field_fwd", ctypes.byref(P), ctypes.byref(S), ctypes.byref(saved.c) if saved is not None else None,

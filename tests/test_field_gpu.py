@@ -71,7 +71,7 @@ def test_field_fwd_matches_operator_path(K, n_rays):
         with torch.no_grad():
             x = ((xyzs - model.xyz_min) / (model.xyz_max - model.xyz_min)).clip(0.0, 1.0)
             enc_ref = model.xyz_encoder(x)
-        assert torch.equal(saved.enc[bases[i]:bases[i] + n], enc_ref)
+        assert torch.equal(saved.rows("enc")[bases[i]:bases[i] + n], enc_ref)
     # padding slots of sigma were not touched
     if K > 1 and bases[1] > counts[0]:
         assert float(sig[counts[0]:bases[1]].max()) == -7.0
