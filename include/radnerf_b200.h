@@ -350,6 +350,31 @@ int rnb_render(const rnb_engine_config* cfg, void* workspace, const void* params
                const float* rays_d, const uint8_t* const* bitfields, const float* bg_host, float* rgb, float* depth,
                float* opacity, float* pass_rgb, int64_t* stats_host, rnb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * (occupancy) MNGP.update_density_grid (networks.py:374-409; NGP :171-201) for all K sub-NeRFs and all
+ *     cascades, without host synchronisation: cell selection (get_all_cells :330-342 in warm-up,
+ *     sample_uniform_and_occupied_cells :344-372 afterwards -- torch.nonzero becomes an ordered device-side
+ *     compaction), density of one jittered point per cell (fused hash encode + geo MLP + exp on tcgen05),
+ *     grid = grid < 0 ? grid : max(grid*decay, new), mean over grid > 0, packbits at min(mean, threshold).
+ *     density_grids[i] (C, G^3) f32 and bitfields[i] (C*G^3/8) u8 are updated in place.
+ *     Random inputs may be supplied for reproducibility / parity tests, or NULL to use the built-in
+ *     counter-based generator seeded with `seed`:
+ *       noise   (K, C, M, 3) f32 in [0,1): jitter inside the cell; M = G^3 (warm-up) or G^3/2 (steady state:
+ *               first G^3/4 uniform cells, then G^3/4 picks among the occupied cells);
+ *       coords1 (K, C, G^3/4, 3) i32 in [0,G): the uniform cells;  pick_u (K, C, G^3/4) f32 in [0,1): the picks
+ *               (cell = occupied[floor(u * n_occupied)], the reference draws randint(n_occupied)).
+ *     The workspace's `tmp` region must be zero before the first call (pass workspace_is_fresh != 0 to have it
+ *     cleared); the library leaves it zero after every call.
+ * ------------------------------------------------------------------------------------ */
+typedef struct {
+  int64_t total_bytes;
+  int64_t tmp, cell_idx, occ_list, block_counts, occ_count, part_sum, part_cnt, mean;
+} rnb_grid_layout;
+int rnb_grid_update_layout_of(const rnb_engine_config* cfg, rnb_grid_layout* out);
+int rnb_grid_update(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* const* density_grids,
+                    uint8_t* const* bitfields, int warmup, float decay, float density_threshold, const float* noise,
+                    const int32_t* coords1, const float* pick_u, uint64_t seed, int workspace_is_fresh, rnb_stream_t stream);
+
 /* Optional per-stage device timing of the fused step (CUDA events around every stage; off by default).
  * Stage order: gate, march, scan, expand, field_fwd, composite_fw, blend_loss, composite_bw, field_bwd,
  * gate_bwd, adam.  rnb_engine_profile_read synchronises, returns the accumulated milliseconds and call

@@ -284,6 +284,130 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
 }
 
 
+// ================================ density of occupancy-grid cells ====================================
+// MNGP.update_density_grid's evaluation step (networks.py:374-399): for every sub-NeRF i and cascade c, a
+// jittered point inside each listed cell -> density_i (hash encode -> geo MLP -> TruncExp) -> scratch grid.
+// Same tile machinery as the forward kernel, cut after the geo network; thread = cell.
+struct GridCellArgs {
+  float* tmp[RNB_MAX_K];       // (C, G^3) f32 scratch grid of sub-NeRF i
+  const int32_t* cell_idx;     // (K, C, M) morton index, < 0 = skip; NULL: all cells, index = m
+  const float* noise;          // (K, C, M, 3) in [0,1); NULL: counter-based generator seeded with `seed`
+  float span[8], half[8];      // per cascade: s_c - s_c/G and s_c/G with s_c = min(2^(c-1), scale)  (networks.py:385-390)
+  int C, G;
+  int64_t M;
+  uint64_t seed;
+};
+
+__device__ __forceinline__ uint32_t tc_compact_bits(uint32_t x) {
+  x = x & 0x49249249u;
+  x = (x | (x >> 2)) & 0xc30c30c3u;
+  x = (x | (x >> 4)) & 0x0f00f00fu;
+  x = (x | (x >> 8)) & 0xff0000ffu;
+  x = (x | (x >> 16)) & 0x0000ffffu;
+  return x;
+}
+// uniform [0,1) from a 64-bit counter (splitmix64 finaliser; 24 mantissa bits)
+__device__ __forceinline__ float tc_counter_uniform(uint64_t seed, uint64_t ctr) {
+  uint64_t z = seed + (ctr + 1) * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(uint32_t)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+__global__ void __launch_bounds__(kWG * 128, 1) density_cells_tc_kernel(TcFieldArgs A, GridCellArgs Q) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, wg = tid >> 7, row = tid & 127, warp = tid >> 5;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcSmem::tmem_slot);
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+  if (tid < kWG) tc::mbar_init(bars + tid, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_d = *tmem_slot + wg * 64;
+  const uint32_t tmem_row = tmem_d + ((uint32_t)((warp & 3) * 32) << 16);
+  unsigned char* a8 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::a8;
+  unsigned char* b16 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::b16;
+  const uint32_t a8_s = tc::smem_u32(a8), b16_s = tc::smem_u32(b16), w_s = tc::smem_u32(smem);
+  uint64_t* bar = bars + wg;
+  uint32_t phase = 0;
+  const int64_t G3 = (int64_t)Q.G * Q.G * Q.G;
+  const int64_t per_pass = (int64_t)Q.C * Q.M;
+  const int64_t n_tiles = (per_pass + kRows - 1) / kRows;
+  const float gm1 = (float)(Q.G - 1);
+  for (int pass = 0; pass < A.K; pass++) {
+    __syncthreads();
+    {
+      const __half* gw = A.geo_w[pass];
+      tc_stage_weight(smem + TcSmem::g1, gw, 64, 32, tid, kWG * 128);
+      tc_stage_weight(smem + TcSmem::g2, gw + 64 * 32, 32, 64, tid, kWG * 128);
+    }
+    tc::fence_async_smem();
+    __syncthreads();
+    for (int64_t tile = (int64_t)blockIdx.x * kWG + wg; tile < n_tiles; tile += (int64_t)gridDim.x * kWG) {
+      const int64_t j = tile * kRows + row;
+      bool valid = j < per_pass;
+      int c = 0;
+      int32_t idx = -1;
+      if (valid) {
+        c = (int)(j / Q.M);
+        const int64_t m = j - (int64_t)c * Q.M;
+        idx = Q.cell_idx ? __ldg(Q.cell_idx + (int64_t)pass * per_pass + j) : (int32_t)m;
+        valid = idx >= 0;
+      }
+      if (valid) {
+        const int64_t e = (int64_t)pass * per_pass + j;
+        float u[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) u[k] = Q.noise ? __ldg(Q.noise + 3 * e + k) : tc_counter_uniform(Q.seed, 3 * (uint64_t)e + k);
+        float p[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          // (coords / (G-1) * 2 - 1) * (s - half) + (rand * 2 - 1) * half, each operation rounded on its own like the ATen chain
+          const float cc = (float)tc_compact_bits((uint32_t)(idx >> k));
+          const float centre = __fmul_rn(__fadd_rn(__fmul_rn(__fdiv_rn(cc, gm1), 2.f), -1.f), Q.span[c]);
+          const float jit = __fmul_rn(__fadd_rn(__fmul_rn(u[k], 2.f), -1.f), Q.half[c]);
+          p[k] = fminf(fmaxf(__fdiv_rn(__fadd_rn(centre, jit) - A.xmin[k], A.xden[k]), 0.f), 1.f);
+        }
+#pragma unroll 1
+        for (int cq = 0; cq < 4; cq++) {
+          uint4 q;
+          q.x = tc_encode_level(A, 4 * cq, p[0], p[1], p[2]); q.y = tc_encode_level(A, 4 * cq + 1, p[0], p[1], p[2]);
+          q.z = tc_encode_level(A, 4 * cq + 2, p[0], p[1], p[2]); q.w = tc_encode_level(A, 4 * cq + 3, p[0], p[1], p[2]);
+          *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, cq)) = q;
+        }
+      } else {
+#pragma unroll
+        for (int cq = 0; cq < 4; cq++) *reinterpret_cast<uint4*>(a8 + tc::tile_chunk_off(kRows, row, cq)) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) tc_fwd_step<false, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::g1, nullptr);
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      tc_relu_row64(tmem_row, b16, row);
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      wg_sync(wg);
+      if (row == 0) tc_fwd_step<false, 32, 64>(bar, tmem_d, b16_s, w_s + TcSmem::g2, nullptr);
+      tc::mbar_wait(bar, phase); phase ^= 1;
+      tc::fence_after_sync();
+      {
+        float v[16];
+        tc::tmem_ld16(tmem_row, v);
+        if (valid) Q.tmp[pass][(int64_t)c * G3 + idx] = expf(__half2float(__float2half_rn(v[0])));
+      }
+      tc::fence_before_sync();
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+}
+
 // ================================ backward on tcgen05 ================================================
 // One persistent CTA per SM: kWGB warpgroups (thread = sample, one 128-sample tile each) plus ONE
 // issuer warp whose elected lane issues every tcgen05.mma of the CTA, so that products accumulating
@@ -717,5 +841,32 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   field_bwd_tc_kernel<<<grid, kWGB * 128 + 32, TcBwdSmem::bytes, as_stream(stream)>>>(
       A, (const __half*)saved->enc, (const __half*)saved->rgb_in, (const __half*)saved->geo_h, (const __half*)saved->rgb_h1,
       (const __half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg);
+  return check_launch(what);
+}
+
+// Density of grid cells for rnb_grid_update (grid.cu).  span/half: per-cascade scalars computed by the caller.
+int rnb_density_cells_tc_launch(const rnb_field_params* P, float* const* tmp, int C, int G, int64_t M, const float* span, const float* half,
+                                const int32_t* cell_idx, const float* noise, uint64_t seed, rnb_stream_t stream) {
+  const char* what = "rnb_grid_update(density)";
+  TcFieldArgs A;
+  RNB_REQUIRE(P != nullptr && P->K >= 1 && P->K <= RNB_MAX_K && P->grid.n_levels == 16 && C >= 1 && C <= 8 && M >= 1, what);
+  if (int rc = to_levels(&P->grid, &A.g, what)) return rc;
+  for (int c = 0; c < 3; c++) { A.xmin[c] = P->xyz_min[c]; A.xden[c] = P->xyz_max[c] - P->xyz_min[c]; }
+  A.table = (const __half2*)P->table_f16;
+  GridCellArgs Q;
+  for (int i = 0; i < P->K; i++) { A.geo_w[i] = (const __half*)P->geo_w_f16[i]; A.rgb_w[i] = nullptr; Q.tmp[i] = tmp[i]; }
+  A.K = P->K;
+  A.rays_o = nullptr; A.rays_d = nullptr; A.ray_id = nullptr; A.ts = nullptr; A.seg = nullptr; A.capacity = 0;
+  for (int c = 0; c < C; c++) { Q.span[c] = span[c]; Q.half[c] = half[c]; }
+  Q.cell_idx = cell_idx; Q.noise = noise; Q.C = C; Q.G = G; Q.M = M; Q.seed = seed;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RNB_CUDA(cudaFuncSetAttribute(density_cells_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem::bytes), what);
+    attr_set = true;
+  }
+  const int64_t tiles = ((int64_t)C * M + kRows - 1) / kRows;
+  int grid = (int)((tiles + kWG - 1) / kWG);
+  if (grid > kNumSMs) grid = kNumSMs;
+  density_cells_tc_kernel<<<grid, kWG * 128, TcSmem::bytes, as_stream(stream)>>>(A, Q);
   return check_launch(what);
 }

@@ -53,6 +53,13 @@ class _RenderLayout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int64) for n in _RENDER_LAYOUT_FIELDS]
 
 
+_GRID_LAYOUT_FIELDS = ["total_bytes", "tmp", "cell_idx", "occ_list", "block_counts", "occ_count", "part_sum", "part_cnt", "mean"]
+
+
+class _GridLayout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int64) for n in _GRID_LAYOUT_FIELDS]
+
+
 class Engine:
     def __init__(self, model, gate=None, n_rays=8192, exp_step_factor=0.0, samples_per_ray=128, max_samples=1024,
                  T_threshold=1e-4, near_distance=0.01, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
@@ -200,6 +207,42 @@ class Engine:
             out["gating_code"] = self.gate_prob
             out["gating_importance"] = self.importance
         return out
+
+    # -- occupancy grids ------------------------------------------------------------------------------------
+    def grids(self):
+        if self.K == 1 and not hasattr(self.model, "size"):
+            return [self.model.density_grid]
+        return [getattr(self.model, f"density_grid_{i}") for i in range(self.K)]
+
+    @torch.no_grad()
+    def update_grid(self, density_threshold, warmup=False, decay=0.95, grids=None, bitfields=None, noise=None, coords1=None,
+                    pick_u=None, seed=None):
+        """MNGP.update_density_grid (networks.py:374-409) for all K sub-NeRFs through rnb_grid_update: no host
+        synchronisation, 6-10 launches.  `grids` / `bitfields` default to the model's buffers (updated in place);
+        noise / coords1 / pick_u are optional explicit random inputs (see include/radnerf_b200.h)."""
+        self.sync_params()
+        if getattr(self, "_grid_ws", None) is None:
+            L = _GridLayout()
+            call("rnb_grid_update_layout_of", ctypes.byref(self.cfg), ctypes.byref(L))
+            self._grid_layout = L
+            self._grid_ws = torch.zeros(L.total_bytes, dtype=torch.uint8, device=self.device)
+            self._grid_calls = 0
+        grids = self.grids() if grids is None else grids
+        bitfields = self.bitfields() if bitfields is None else bitfields
+        for g in grids:
+            _lib.check_input(g, "density_grid", torch.float32)
+        g_arr = (ctypes.c_void_p * self.K)(*[g.data_ptr() for g in grids])
+        b_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bitfields])
+        self._grid_calls += 1
+        if seed is None:
+            seed = 0x5EED0000 + self._grid_calls
+        call("rnb_grid_update", ctypes.byref(self.cfg), self._grid_ws, self.flat16, g_arr, b_arr, i32(1 if warmup else 0),
+             f32(decay), f32(density_threshold), noise, coords1, pick_u, ctypes.c_uint64(seed), i32(0), stream_arg(self.device))
+
+    def grid_mean(self):
+        """mean density over grid > 0 of the last update, per sub-NeRF (device tensor view)."""
+        L = self._grid_layout
+        return self._grid_ws[L.mean:L.mean + 4 * self.K].view(torch.float32)
 
     # -- test-time rendering ----------------------------------------------------------------------------------
     def _render_plan(self, n_rays, samples_per_ray):

@@ -68,6 +68,17 @@ class Trainer:
     def _grid_update(self):
         thr = syn.DENSITY_THRESHOLD
         warm = self.global_step < self.warmup_steps
+        if self.engine is not None:
+            # fused update (csrc/grid.cu).  Benchmark mode runs the SAME work against shadow buffers so that the
+            # occupancy used for marching -- and therefore the samples per ray -- stays that of the synthetic scene.
+            if not self.freeze_occupancy:
+                self.engine.update_grid(thr, warmup=warm)
+                return
+            if self._shadow is None:
+                self._shadow = ([torch.zeros_like(g) for g in self.engine.grids()],
+                                [torch.zeros_like(b) for b in self.engine.bitfields()])
+            self.engine.update_grid(thr, warmup=warm, grids=self._shadow[0], bitfields=self._shadow[1])
+            return
         if not self.freeze_occupancy:
             self.model.update_density_grid(thr, warmup=warm)
             return
