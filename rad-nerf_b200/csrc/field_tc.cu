@@ -77,10 +77,12 @@ struct TcSmem {
   static constexpr int r2 = r1 + 64 * 32 * 2;  // 64 x 64
   static constexpr int r3 = r2 + 64 * 64 * 2;  // 16 x 64
   static constexpr int wend = r3 + 16 * 64 * 2;
-  // per warpgroup: a 128x32 operand tile (encoding, then rgb input) and a 128x64 tile (hidden activations)
+  // per warpgroup: a 128x32 operand tile (encoding, then rgb input) and two 128x64 tiles (hidden activations; the
+  // second one takes rgb hidden 2 so that the bulk store of rgb hidden 1 never races with the next epilogue)
   static constexpr int a8 = 0;
   static constexpr int b16 = kRows * 32 * 2;
-  static constexpr int per_wg = b16 + kRows * 64 * 2;
+  static constexpr int b16b = b16 + kRows * 64 * 2;
+  static constexpr int per_wg = b16b + kRows * 64 * 2;
   static constexpr int wg0 = (wend + 127) / 128 * 128;
   static constexpr int bars = wg0 + kWG * per_wg;       // kWG mbarriers
   static constexpr int tmem_slot = bars + kWG * 8;
@@ -120,18 +122,18 @@ __device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* til
 
 // One layer step of the forward chain, executed by the warpgroup's elected thread: issue the layer's MMAs and, when
 // activations are saved for the backward pass, copy the operand tile the MMAs read -- it already has the layout the
-// backward kernel wants -- to global memory with one bulk store.  The warpgroup's mbarrier completes when the MMAs
-// are done AND the store has finished reading the tile (2 arrivals), after which the tile may be overwritten.
+// backward kernel wants -- to global memory with one bulk store.  A tile is overwritten at the earliest in the
+// epilogue of the FOLLOWING step; this thread confirms that the previous step's store has finished reading its tile
+// before it issues (and commits) this step's MMAs, and everybody waits for those, so no extra signalling is needed.
 template <bool kSave, int N, int KDIM>
 __device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint32_t a_smem, uint32_t w_smem, __half* save_tile) {
+  if (kSave) tc::bulk_wait_read();
   tc::fence_after_sync();
   tc_layer_mma<N, KDIM>(tmem_d, a_smem, w_smem);
   tc::mma_commit(bar);
   if (kSave) {
     tc::bulk_store(save_tile, a_smem, kRows * KDIM * 2);
     tc::bulk_commit();
-    tc::bulk_wait_read();
-    tc::mbar_arrive(bar);
   }
 }
 
@@ -145,7 +147,7 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcSmem::tmem_slot);
   if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
-  if (tid < kWG) tc::mbar_init(bars + tid, kSave ? 2 : 1);
+  if (tid < kWG) tc::mbar_init(bars + tid, 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   tc::fence_before_sync();
   __syncthreads();
@@ -154,7 +156,8 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
   const uint32_t tmem_row = tmem_d + ((uint32_t)((warp & 3) * 32) << 16);     // + this warp's 32 lanes
   unsigned char* a8 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::a8;
   unsigned char* b16 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::b16;
-  const uint32_t a8_s = tc::smem_u32(a8), b16_s = tc::smem_u32(b16), w_s = tc::smem_u32(smem);
+  unsigned char* b16b = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::b16b;
+  const uint32_t a8_s = tc::smem_u32(a8), b16_s = tc::smem_u32(b16), b16b_s = tc::smem_u32(b16b), w_s = tc::smem_u32(smem);
   uint64_t* bar = bars + wg;
   uint32_t phase = 0;
   const int K = A.K;
@@ -257,12 +260,12 @@ __global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs 
       if (row == 0) tc_fwd_step<kSave, 64, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r2, s_rgb_h1 + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
-      tc_relu_row64(tmem_row, b16, row);
+      tc_relu_row64(tmem_row, b16b, row);
       // ---- rgb layer 3: 64 -> 16, sigmoid ----
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64);
+      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16b_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       {
@@ -528,7 +531,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
     TcFieldArgs A, const __half* __restrict__ s_enc, const __half* __restrict__ s_rgb_in, const __half* __restrict__ s_geo_h,
     const __half* __restrict__ s_rgb_h1, const __half* __restrict__ s_rgb_h2, const __half* __restrict__ s_sraw,
     const __half* __restrict__ rgb4, const float* __restrict__ dsig, const float* __restrict__ drgb, float gs,
-    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels) {
+    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels, int agg_long_res) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool is_issuer = warp == kWGB * 4;
@@ -744,8 +747,8 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
             const float d0 = d.x * inv_gs, d1 = d.y * inv_gs;
             float* gl = grad_table + 2 * (size_t)off;
             if (l < n_aggregate_levels) {   // warp-uniform
-#pragma unroll
-              for (int k = 0; k < 8; k++) scatter_aggregated(gl, L.idx[k], L.w[k] * d0, L.w[k] * d1, valid);
+              if (A.g.res[l] <= (uint32_t)agg_long_res) scatter_level_aggregated<5>(gl, L, d0, d1, valid);
+              else scatter_level_aggregated<3>(gl, L, d0, d1, valid);
             } else if (valid) {
 #pragma unroll
               for (int k = 0; k < 8; k++) red_add_f32x2(gl + 2 * (size_t)L.idx[k], L.w[k] * d0, L.w[k] * d1);
@@ -830,6 +833,9 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   for (int l = 0; l < A.g.n_levels; l++)
     if (A.g.res[l] <= 128) n_agg = l + 1;
   if (const char* e = getenv("RNB_AGG_LEVELS")) n_agg = atoi(e);   // tuning knob (profiles/): levels with warp-aggregated reductions
+  while (n_agg > 0 && A.g.res[n_agg - 1] >= 1024) n_agg--;          // the cell key holds 10-11 bits per axis
+  int agg_long_res = 48;                                            // levels up to this resolution combine whole-warp runs
+  if (const char* e = getenv("RNB_AGG_LONG_RES")) agg_long_res = atoi(e);
   static bool attr_set = false;
   if (!attr_set) {
     RNB_CUDA(cudaFuncSetAttribute(field_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcBwdSmem::bytes), what);
@@ -840,7 +846,8 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   if (grid > kNumSMs) grid = kNumSMs;
   field_bwd_tc_kernel<<<grid, kWGB * 128 + 32, TcBwdSmem::bytes, as_stream(stream)>>>(
       A, (const __half*)saved->enc, (const __half*)saved->rgb_in, (const __half*)saved->geo_h, (const __half*)saved->rgb_h1,
-      (const __half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg);
+      (const __half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg,
+      agg_long_res);
   return check_launch(what);
 }
 

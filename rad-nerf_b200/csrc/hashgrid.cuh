@@ -113,6 +113,7 @@ namespace rnb {
 struct LevelCorners {
   uint32_t idx[8];
   float w[8];
+  uint32_t cell;   // cx | cy << 11 | cz << 22: identifies the cell on levels with res < 1024
 };
 
 __device__ __forceinline__ LevelCorners level_corners(float x, float y, float z, float scale, uint32_t res, uint32_t size) {
@@ -122,6 +123,7 @@ __device__ __forceinline__ LevelCorners level_corners(float x, float y, float z,
   const uint32_t cx = (uint32_t)(int)fx, cy = (uint32_t)(int)fy, cz = (uint32_t)(int)fz;
   const float wx1 = px - fx, wy1 = py - fy, wz1 = pz - fz;
   const float wx0 = 1.f - wx1, wy0 = 1.f - wy1, wz0 = 1.f - wz1;
+  L.cell = cx | (cy << 11) | (cz << 22);
   // weight of corner k = (x-term) * (y-term) * (z-term), evaluated in the same order as hashgrid_fwd_kernel
   const float xy00 = wx0 * wy0, xy10 = wx1 * wy0, xy01 = wx0 * wy1, xy11 = wx1 * wy1;
   L.w[0] = xy00 * wz0; L.w[1] = xy10 * wz0; L.w[2] = xy01 * wz0; L.w[3] = xy11 * wz0;
@@ -146,6 +148,33 @@ __device__ __forceinline__ LevelCorners level_corners(float x, float y, float z,
     L.idx[4] = (cx ^ y0 ^ z1) % size; L.idx[5] = (x1 ^ y0 ^ z1) % size; L.idx[6] = (cx ^ y1 ^ z1) % size; L.idx[7] = (x1 ^ y1 ^ z1) % size;
   }
   return L;
+}
+
+// The same for all 8 corners of one level at once.  Lanes in the same CELL share all eight corner entries, so the
+// run structure (heads, reach of every shuffle step) is computed once per level from the cell key instead of once
+// per corner.  kSteps = 5 combines whole-warp runs; kSteps = 3 cuts runs at 8-lane boundaries (fine levels, where a
+// ray spends only a few samples per cell: fewer shuffles for at most a few extra reductions).
+template <int kSteps>
+__device__ __forceinline__ void scatter_level_aggregated(float* grad_level, const LevelCorners& L, float d0, float d1, bool active) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t key = active ? L.cell : 0xffffffffu;
+  const uint32_t prev = __shfl_up_sync(kFullMask, key, 1);
+  const unsigned heads = __ballot_sync(kFullMask, lane == 0 || prev != key || (kSteps < 5 && (lane & ((1 << kSteps) - 1)) == 0));
+  const unsigned after = (heads >> lane) >> 1;          // run heads strictly behind this lane
+  bool take[kSteps];
+#pragma unroll
+  for (int j = 0; j < kSteps; j++) take[j] = lane + (1 << j) < 32 && (after & ((1u << (1 << j)) - 1u)) == 0u;
+  const bool emit = active && ((heads >> lane) & 1u);
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    float g0 = L.w[k] * d0, g1 = L.w[k] * d1;
+#pragma unroll
+    for (int j = 0; j < kSteps; j++) {
+      const float v0 = __shfl_down_sync(kFullMask, g0, 1 << j), v1 = __shfl_down_sync(kFullMask, g1, 1 << j);
+      if (take[j]) { g0 += v0; g1 += v1; }
+    }
+    if (emit) red_add_f32x2(grad_level + 2 * (size_t)L.idx[k], g0, g1);
+  }
 }
 
 }  // namespace rnb

@@ -69,10 +69,27 @@ __device__ __forceinline__ int march_ray_warp(const Ray& ray, const MarchParams&
   while (true) {
     // ---- chain: lane j <- c_j ------------------------------------------------------------
     float mine = tc;
+    bool fast = false;
+    if (kConstDt) {
+      // Constant step: while the chunk stays inside one binade [2^e, 2^(e+1)) every c_k is a multiple of u = ulp(2^e),
+      // so fl(c_k + dt) = c_k + q with q = dt rounded to a multiple of u -- the same q for every k (barring an exact
+      // tie |dt - q| = u/2, where round-to-even would depend on c_k).  Then c_j = c_0 + j*q exactly (one FMA, no
+      // rounding: the value is a multiple of u below 2^(e+1)) and the 31 dependent additions collapse.
+      const float c1 = __fadd_rn(tc, p.dt_min);
+      const float q = __fsub_rn(c1, tc);
+      const float c31 = __fmaf_rn(31.0f, q, tc);
+      const uint32_t eb = __float_as_uint(tc) & 0x7f800000u;
+      const float half_ulp = __uint_as_float(eb - (24u << 23));
+      fast = eb > (24u << 23) && eb == (__float_as_uint(c1) & 0x7f800000u) && eb == (__float_as_uint(c31) & 0x7f800000u) &&
+             fabsf(__fsub_rn(p.dt_min, q)) != half_ulp;
+      if (fast) mine = __fmaf_rn((float)lane, q, tc);
+    }
+    if (!fast) {
 #pragma unroll
-    for (int k = 1; k < 32; k++) {
-      const float d = kConstDt ? p.dt_min : calc_dt(mine, p);
-      if (k <= lane) mine = __fadd_rn(mine, d);
+      for (int k = 1; k < 32; k++) {
+        const float d = kConstDt ? p.dt_min : calc_dt(mine, p);
+        if (k <= lane) mine = __fadd_rn(mine, d);
+      }
     }
     const float my_dt = kConstDt ? p.dt_min : calc_dt(mine, p);
     const bool valid = mine < t2;
