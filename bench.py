@@ -214,17 +214,61 @@ def run_product(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
 
+    ahead = tr.engine is not None and not args.no_march_ahead
+
+    def flush_l2():
+        # evict L2 between steps (inputs are smaller than L2).  When the next batch is marched ahead on the side stream,
+        # that work must be finished before the flush starts: otherwise it could hide behind the flush, whose time is
+        # subtracted below, and the step would look faster than it is.
+        if ahead and tr.engine._march_stream is not None:
+            torch.cuda.current_stream().wait_stream(tr.engine._march_stream)
+        flush.add_(1.0)
+
     def dev_step(s):
-        flush.add_(1.0)     # evict L2 between steps (inputs are smaller than L2)
+        flush_l2()
+        nxt = dev[(s + 1) % len(dev)]
+        tr.step(*dev[s % len(dev)], next_rays=nxt[:2] if ahead else None)
+
+    def plain_step(s):      # no marching ahead: clean per-stage times for the roofline leg
+        flush.add_(1.0)
         tr.step(*dev[s % len(dev)])
 
     losses = []
+    staged = {}
+    loss_pin = torch.zeros(4, 8, dtype=torch.float32).pin_memory()      # ring of pinned read-back slots
+    loss_evt = [None] * 4
+
+    def read_back(s, loss_vec):
+        # device->host read of every step's loss: an asynchronous copy into pinned memory, consumed one step later so that
+        # the host keeps launching ahead (what a training loop that logs its loss does); the last ones are drained below
+        k = s % 4
+        loss_pin[k].copy_(loss_vec, non_blocking=True)
+        ev = torch.cuda.Event(); ev.record(); loss_evt[k] = ev
+        j = (s - 1) % 4
+        if s > 0 and loss_evt[j] is not None:
+            loss_evt[j].synchronize()
+            losses.append(float(loss_pin[j][0]))
 
     def e2e_step(s):
-        flush.add_(1.0)
-        o, d, t = (a.cuda(non_blocking=True) for a in host[s % len(host)])
-        losses.append(float(tr.step(o, d, t)))      # device->host read of the step's loss
+        # every step uploads ONE batch from pinned host memory (the next one when marching ahead, so that its rays are
+        # on the device in time) and reads the step's loss back
+        flush_l2()
+        if not ahead:
+            o, d, t = (a.cuda(non_blocking=True) for a in host[s % len(host)])
+            tr.step(o, d, t)
+        else:
+            if s not in staged:
+                staged[s] = tuple(a.cuda(non_blocking=True) for a in host[s % len(host)])
+            staged[s + 1] = tuple(a.cuda(non_blocking=True) for a in host[(s + 1) % len(host)])
+            o, d, t = staged.pop(s)
+            tr.step(o, d, t, next_rays=staged[s + 1][:2])
+        read_back(s, tr.engine.loss if tr.engine is not None else tr.last_loss.reshape(1).expand(8))
 
+    if ahead and os.environ.get("RNB_BENCH_PRIO", "1") == "1":
+        # the step runs on a high-priority stream: the side stream that marches the next batch then only fills what the
+        # step's own kernels leave free instead of delaying them
+        torch.cuda.synchronize()
+        torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
     for s in range(args.warmup):
         dev_step(s)
     # time the L2 flush alone so that it can be subtracted (it is not part of the step)
@@ -239,8 +283,10 @@ def run_product(args):
     # per-stage device time of the same steps (separate pass: CUDA events around every stage of the fused step)
     stage_ms = {}
     if tr.engine is not None:
+        tr.engine._ahead.clear()
+        torch.cuda.synchronize()
         lib.rnb_engine_profile(1)
-        timed(dev_step, args.steps)
+        timed(plain_step, args.steps)
         arr_ms = (ctypes.c_double * 16)(); arr_n = (ctypes.c_int32 * 16)()
         lib.rnb_engine_profile_read(arr_ms, arr_n, 16)
         lib.rnb_engine_profile(0)
@@ -259,10 +305,11 @@ def run_product(args):
             "config": {"workload": args.workload, "K": K, "scale": w["scale"], "batch_rays_per_gpu": BATCH,
                        "params": "tcnn-style random init",
                        "occupancy": "analytic scene, fixed; grid update every 16 steps runs on shadow grids",
-                       "l2": "flushed between steps (256 MiB write, its time subtracted)", "parallelism": f"ray-sharded dp{world}",
+                       "l2": "flushed between steps (256 MiB write, its time subtracted)",
+                       "march_ahead": bool(ahead), "parallelism": f"ray-sharded dp{world}",
                        "path": "fused engine (rnb_engine_*)" if tr.engine is not None else "python operator surface"},
             "clocks": clk,
-            "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * BATCH * 12, "d2h_bytes_per_step": 4,
+            "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * BATCH * 12, "d2h_bytes_per_step": 32,
                     "ms_per_step": e2e_ms},
             "gpu_launches": launches, "final_loss": losses[-1] if losses else None}
     if tr.engine is not None:
@@ -309,6 +356,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="radnerf_tat_k2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-march-ahead", action="store_true", help="march every batch inside its own step (single stream)")
     ap.add_argument("--python-surface", action="store_true", help="time the drop-in Python operator surface instead of the fused engine")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

@@ -298,6 +298,9 @@ typedef struct {
   int64_t d_pass_opacity, d_pass_depth, d_pass_rgb;        /* gradient seeds, same shapes                     */
   int64_t rgb, opacity, depth;   /* results: f32 (R,3) | f32 (R) | f32 (R,K)  (ml_rendering.py:72-77)         */
   int64_t loss;                  /* f32 (8): [total, rgb, opacity, cv_importance, depth_mutual, -, -, -]      */
+  int64_t march_slot1;           /* second copy of the marcher's outputs [t_scratch .. deltas] (same internal offsets,
+                                  * march_slot_bytes long) for marching the NEXT batch while this one trains      */
+  int64_t march_slot_bytes;
 } rnb_engine_layout;
 
 int rnb_engine_layout_of(const rnb_engine_config* cfg, rnb_engine_layout* out);
@@ -314,7 +317,15 @@ int rnb_engine_gate(const rnb_engine_config* cfg, void* workspace, const void* p
 int rnb_engine_fwd_bwd(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* grads_f32,
                        const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
                        const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
-                       const float* importance, int with_backward, rnb_stream_t stream);
+                       const float* importance, int with_backward, int march_slot, rnb_stream_t stream);
+/* Marching depends on the rays and the occupancy bitfields only, not on the parameters: the samples of the NEXT
+ * batch can be produced on a second stream while the current batch is in its field / backward kernels.
+ * rnb_engine_march runs AABB + march + scan + expand for one batch into workspace slot `slot` (0 or 1);
+ * rnb_engine_fwd_bwd(march_slot = that slot) then skips its own marching (noise / bitfields may be NULL).
+ * march_slot = -1: march inline into slot 0 (the default, single-stream behaviour).  The caller orders the
+ * two streams (events) and must not update the bitfields between the two calls. */
+int rnb_engine_march(const rnb_engine_config* cfg, void* workspace, const float* rays_o, const float* rays_d,
+                     const float* noise, const uint8_t* const* bitfields, int slot, rnb_stream_t stream);
 /* Phase 3: Adam (torch.optim.Adam semantics, no weight decay) over the flat vector; writes the fp16 copy
  * and ZEROES the gradient for the next step.  grad_scale multiplies the gradient first. */
 int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq,

@@ -427,6 +427,8 @@ int rnb_engine_layout_of(const rnb_engine_config* c, rnb_engine_layout* L) {
   L->d_pass_opacity = w.take(K * R * 4); L->d_pass_depth = w.take(K * R * 4); L->d_pass_rgb = w.take(K * R * 3 * 4);
   L->rgb = w.take(R * 3 * 4); L->opacity = w.take(R * 4); L->depth = w.take(R * K * 4);
   L->loss = w.take(8 * 4);
+  L->march_slot_bytes = L->enc - L->t_scratch;     // [t_scratch, counts, starts, seg, ray_id, ts, deltas] are contiguous
+  L->march_slot1 = w.take(L->march_slot_bytes);
   L->total_bytes = w.off;
   return RNB_OK;
 }
@@ -460,29 +462,20 @@ int rnb_engine_gate(const rnb_engine_config* c, void* workspace, const void* par
                       ws + L.gate_logits, (float*)(ws + L.gate_prob), (float*)(ws + L.importance), stream);
 }
 
-int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32,
-                       const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
-                       const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
-                       const float* importance, int with_backward, rnb_stream_t stream) {
-  const char* what = "rnb_engine_fwd_bwd";
+int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* rays_o, const float* rays_d, const float* noise,
+                     const uint8_t* const* bitfields, int slot, rnb_stream_t stream) {
+  const char* what = "rnb_engine_march";
   if (int rc = check_cfg(c, what)) return rc;
-  RNB_REQUIRE(workspace && params_f16 && rays_o && rays_d && target_rgb && noise && bitfields && bg_host, what);
-  RNB_REQUIRE(n_rays_global >= c->n_rays && (c->K == 1 || importance != nullptr), what);
-  RNB_REQUIRE(!with_backward || grads_f32 != nullptr, what);
+  RNB_REQUIRE(workspace && rays_o && rays_d && noise && bitfields && (slot == 0 || slot == 1), what);
   rnb_engine_layout L;
   rnb_engine_layout_of(c, &L);
-  char* ws = (char*)workspace;
+  char* ws = (char*)workspace + (slot == 1 ? L.march_slot1 - L.t_scratch : 0);
   cudaStream_t st = as_stream(stream);
   const int R = c->n_rays, K = c->K;
   const int64_t S = c->sample_capacity;
-  const __half* p16 = (const __half*)params_f16;
   int32_t* counts = (int32_t*)(ws + L.counts); int32_t* starts = (int32_t*)(ws + L.starts); int32_t* seg = (int32_t*)(ws + L.seg);
   float* t_scratch = (float*)(ws + L.t_scratch);
   int32_t* ray_id = (int32_t*)(ws + L.ray_id); float* ts = (float*)(ws + L.ts); float* deltas = (float*)(ws + L.deltas);
-  float* sigmas = (float*)(ws + L.sigmas); __half* rgb4 = (__half*)(ws + L.rgb4); float* wsamp = (float*)(ws + L.ws);
-
-  RNB_CUDA(cudaMemsetAsync(ws + L.loss, 0, 8 * 4, st), what);
-  // 1. march all K passes (AABB inline), 2. scan, 3. expand
   const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, c->scale);
   BitfieldPtrs bf;
   for (int i = 0; i < K; i++) { RNB_REQUIRE(bitfields[i] != nullptr, what); bf.p[i] = bitfields[i]; }
@@ -498,7 +491,41 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
   }
   { StageTimer tm(ST_SCAN, st); eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg); }
   { StageTimer tm(ST_EXPAND, st); eng_expand_kernel<<<ray_grid, 256, 0, st>>>(counts, starts, t_scratch, mp, R, S, ray_id, ts, deltas); }
-  if (int rc = check_launch(what)) return rc;
+  return check_launch(what);
+}
+
+int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32,
+                       const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
+                       const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
+                       const float* importance, int with_backward, int march_slot, rnb_stream_t stream) {
+  const char* what = "rnb_engine_fwd_bwd";
+  if (int rc = check_cfg(c, what)) return rc;
+  RNB_REQUIRE(workspace && params_f16 && rays_o && rays_d && target_rgb && bg_host, what);
+  RNB_REQUIRE(n_rays_global >= c->n_rays && (c->K == 1 || importance != nullptr), what);
+  RNB_REQUIRE(!with_backward || grads_f32 != nullptr, what);
+  rnb_engine_layout L;
+  rnb_engine_layout_of(c, &L);
+  char* ws = (char*)workspace;
+  cudaStream_t st = as_stream(stream);
+  const int R = c->n_rays, K = c->K;
+  const int64_t S = c->sample_capacity;
+  const __half* p16 = (const __half*)params_f16;
+  float* sigmas = (float*)(ws + L.sigmas); __half* rgb4 = (__half*)(ws + L.rgb4); float* wsamp = (float*)(ws + L.ws);
+
+  RNB_REQUIRE(march_slot >= -1 && march_slot <= 1, what);
+  // the marcher's outputs live in one of two slots (see rnb_engine_march)
+  const int64_t slot_off = march_slot == 1 ? L.march_slot1 - L.t_scratch : 0;
+  int32_t* counts = (int32_t*)(ws + slot_off + L.counts); int32_t* starts = (int32_t*)(ws + slot_off + L.starts);
+  int32_t* seg = (int32_t*)(ws + slot_off + L.seg);
+  int32_t* ray_id = (int32_t*)(ws + slot_off + L.ray_id); float* ts = (float*)(ws + slot_off + L.ts); float* deltas = (float*)(ws + slot_off + L.deltas);
+  RNB_CUDA(cudaMemsetAsync(ws + L.loss, 0, 8 * 4, st), what);
+  // 1. march all K passes (AABB inline), 2. scan, 3. expand -- unless the batch was marched ahead of time
+  const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, c->scale);
+  const dim3 ray_grid(ceil_div((int64_t)R * 32, 256), K);
+  if (march_slot < 0) {
+    RNB_REQUIRE(noise && bitfields, what);
+    if (int rc = rnb_engine_march(c, workspace, rays_o, rays_d, noise, bitfields, 0, stream)) return rc;
+  }
   // 4. field forward
   rnb_field_params P;
   P.K = K; P.grid = c->grid;

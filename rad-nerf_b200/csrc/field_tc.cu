@@ -138,7 +138,7 @@ __device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint
 }
 
 template <bool kSave>
-__global__ void __launch_bounds__(kWG * 128, 1) field_fwd_tc_kernel(TcFieldArgs A, __half* __restrict__ s_enc, __half* __restrict__ s_rgb_in,
+__global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __restrict__ s_enc, __half* __restrict__ s_rgb_in,
                                                                      __half* __restrict__ s_geo_h, __half* __restrict__ s_rgb_h1,
                                                                      __half* __restrict__ s_rgb_h2, __half* __restrict__ s_sraw,
                                                                      float* __restrict__ sigmas, __half* __restrict__ rgb4) {

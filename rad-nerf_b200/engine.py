@@ -38,7 +38,7 @@ class _Config(ctypes.Structure):
 _LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_hidden", "gate_logits", "gate_dlogits", "gate_prob", "dgate", "importance",
                   "t_scratch", "counts", "starts", "seg", "ray_id", "ts", "deltas", "enc", "rgb_in", "geo_h", "rgb_h1", "rgb_h2",
                   "sraw", "sigmas", "rgb4", "ws", "dsigmas", "drgbs", "pass_opacity", "pass_depth", "pass_rgb", "pass_total",
-                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss"]
+                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss", "march_slot1", "march_slot_bytes"]
 
 
 class _Layout(ctypes.Structure):
@@ -135,6 +135,10 @@ class Engine:
         self.lr, self.betas, self.eps = lr, betas, eps
         self.opt_step = 0
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        # marching ahead (rnb_engine_march): the next batch's samples are produced on a side stream into the other slot
+        self._march_stream = None
+        self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
+        self._slot = 0                  # slot holding the samples of the batch last trained on
 
     def _view(self, name, dtype, shape):
         off = getattr(self.layout, name)
@@ -156,14 +160,71 @@ class Engine:
             return [self.model.density_bitfield]
         return [getattr(self.model, f"density_bitfield_{i}") for i in range(self.K)]
 
+    def _slot_view(self, name, dtype, shape, slot):
+        v = self._view(name, dtype, shape)
+        if slot == 0:
+            return v
+        L = self.layout
+        off = L.march_slot1 + (getattr(L, name) - L.t_scratch)
+        return self.ws[off:off + v.numel() * v.element_size()].view(dtype).view(*shape)
+
     # -- phases -------------------------------------------------------------------------------------------
+    def prefetch(self, rays_o, rays_d, noise=None):
+        """March the NEXT batch (AABB, march, scan, expand: everything that depends on rays and occupancy only) on a
+        side stream while the kernels of the current step run.  Call it BEFORE step() of the current batch; the
+        following step()/forward_backward() on these same tensors picks the samples up.  The bitfields must not
+        change in between (the trainer does not prefetch across an occupancy update)."""
+        _lib.check_input(rays_o, "rays_o", torch.float32)
+        _lib.check_input(rays_d, "rays_d", torch.float32)
+        assert rays_o.shape[0] == self.n_rays
+        while len(self._ahead) > 1:             # never picked up: let it finish, then forget it
+            torch.cuda.current_stream(self.device).wait_event(self._ahead.pop(next(iter(self._ahead)))[4])
+        if noise is None:
+            noise = torch.rand(self.K, self.n_rays, device=self.device)
+        if self._march_stream is None:
+            self._march_stream = torch.cuda.Stream(self.device)
+        # the batch about to be trained sits in the slot of its own prefetch, or will be marched inline into slot 0
+        busy = next(iter(self._ahead.values()))[0] if self._ahead else 0
+        slot = busy ^ 1
+        cur = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)                       # inputs produced / the slot's previous reader (two steps back) finished
+        bfs = self.bitfields()
+        bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
+        with torch.cuda.stream(self._march_stream):
+            self._march_stream.wait_event(ready)
+            call("rnb_engine_march", ctypes.byref(self.cfg), self.ws, rays_o, rays_d, noise, bf_arr, i32(slot),
+                 stream_arg(self.device))
+            done = torch.cuda.Event()
+            done.record(self._march_stream)
+        self._ahead[(rays_o.data_ptr(), rays_d.data_ptr())] = (slot, rays_o, rays_d, noise, done)
+
     def forward_backward(self, rays_o, rays_d, target_rgb, noise, bg, with_backward=True):
         """noise (K,R) f32 in [0,1); bg: K x 3 python floats.  Fills the result views and, with
         `with_backward`, accumulates into self.grads.  Returns nothing; no host synchronisation."""
         c = self.cfg
-        for t, n in ((rays_o, "rays_o"), (rays_d, "rays_d"), (target_rgb, "target_rgb"), (noise, "noise")):
+        for t, n in ((rays_o, "rays_o"), (rays_d, "rays_d"), (target_rgb, "target_rgb")):
             _lib.check_input(t, n, torch.float32)
-        assert rays_o.shape[0] == self.n_rays and noise.numel() == self.K * self.n_rays
+        assert rays_o.shape[0] == self.n_rays
+        cur = torch.cuda.current_stream(self.device)
+        hit = self._ahead.pop((rays_o.data_ptr(), rays_d.data_ptr()), None)
+        if hit is not None:
+            march_slot, _, _, noise, done = hit
+            cur.wait_event(done)
+            _lib.launch_count -= 3      # the march / scan / expand launches were counted with rnb_engine_march
+        else:
+            # not marched ahead: march here, into the slot no prefetch is using.  Entries older than the newest one
+            # were never picked up (the caller changed its mind): let them finish, then forget them.
+            keys = list(self._ahead)
+            for k in keys[:-1]:
+                cur.wait_event(self._ahead.pop(k)[4])
+            march_slot = (self._ahead[keys[-1]][0] ^ 1) if keys else 0
+            if noise is None:
+                noise = torch.rand(self.K, self.n_rays, device=self.device)
+            _lib.check_input(noise, "noise", torch.float32)
+            assert noise.numel() == self.K * self.n_rays
+        self._slot = march_slot
+        inline = hit is None
         st = stream_arg(self.device)
         if self.K > 1:
             call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
@@ -172,9 +233,12 @@ class Engine:
         bfs = self.bitfields()
         bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
         bg_arr = (ctypes.c_float * (3 * self.K))(*[float(x) for row in bg for x in row])
+        if inline:
+            call("rnb_engine_march", ctypes.byref(c), self.ws, rays_o, rays_d, noise, bf_arr, i32(march_slot), st)
+            _lib.launch_count -= 3
         call("rnb_engine_fwd_bwd", ctypes.byref(c), self.ws, self.flat16, self.grads if with_backward else None,
              rays_o, rays_d, target_rgb, noise, bf_arr, bg_arr, i64(self.n_rays * self.world),
-             self.importance if self.K > 1 else None, i32(1 if with_backward else 0), st)
+             self.importance if self.K > 1 else None, i32(1 if with_backward else 0), i32(march_slot), st)
 
     def adam_step(self, lr=None):
         if self.world > 1:
@@ -193,8 +257,6 @@ class Engine:
 
     def step(self, rays_o, rays_d, target_rgb, lr=None, random_bg=False, noise=None):
         """One training step.  Returns the loss vector view [total, rgb, opacity, cv, depth_mutual, ...] (device)."""
-        if noise is None:
-            noise = torch.rand(self.K, self.n_rays, device=self.device)
         self.forward_backward(rays_o, rays_d, target_rgb, noise, self.background(random_bg), True)
         self.adam_step(lr)
         return self.loss
@@ -296,6 +358,6 @@ class Engine:
 
     def sample_stats(self):
         """(samples per pass list, overflow flag) -- synchronises."""
-        seg = self.seg.tolist()
+        seg = self._slot_view("seg", torch.int32, (2 * MAX_K + 4,), self._slot).tolist()
         K = self.K
         return seg[K + 1:2 * K + 1], bool(seg[2 * K + 1])

@@ -98,10 +98,15 @@ class Trainer:
             setattr(self.model, n, keep[n])
 
     # -- one step ----------------------------------------------------------------------------
-    def step(self, rays_o, rays_d, target_rgb):
-        """rays_o, rays_d, target_rgb: (B_local,3) fp32 CUDA tensors.  Returns the (unscaled) loss tensor."""
+    def step(self, rays_o, rays_d, target_rgb, next_rays=None):
+        """rays_o, rays_d, target_rgb: (B_local,3) fp32 CUDA tensors.  Returns the (unscaled) loss tensor.
+        next_rays = (rays_o, rays_d) of the FOLLOWING batch, when it is already on the device: its marching then
+        overlaps this step's field kernels (Engine.prefetch).  Skipped when the following step starts with an
+        occupancy update, so that every batch is marched against the same bitfields as in the sequential order."""
         if self.global_step % self.update_interval == 0:
             self._grid_update()
+        if self.engine is not None and next_rays is not None and (self.global_step + 1) % self.update_interval != 0:
+            self.engine.prefetch(next_rays[0], next_rays[1])
         if self.engine is not None:
             loss = self.engine.step(rays_o, rays_d, target_rgb, lr=self.lr, random_bg=self.random_bg)
             self.global_step += 1
@@ -140,4 +145,5 @@ class Trainer:
         self.opt.step()
         self.global_step += 1
         self.last_results = results
-        return loss.detach()
+        self.last_loss = loss.detach()
+        return self.last_loss
