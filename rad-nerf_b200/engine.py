@@ -16,7 +16,7 @@ import ctypes
 import torch
 import torch.distributed as dist
 
-from . import _lib
+from . import _lib, parallel
 from ._lib import call, f32, i32, i64, stream_arg
 from .field import MAX_K
 from .tcnn import _GridMeta
@@ -134,7 +134,7 @@ class Engine:
         self.loss = v("loss", torch.float32, (8,))
         self.lr, self.betas, self.eps = lr, betas, eps
         self.opt_step = 0
-        self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        self.world = parallel.world_size()
         # marching ahead (rnb_engine_march): the next batch's samples are produced on a side stream into the other slot
         self._march_stream = None
         self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
@@ -228,8 +228,7 @@ class Engine:
         st = stream_arg(self.device)
         if self.K > 1:
             call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
-            if self.world > 1:      # CV loss is non-linear in the batch: the importance must be global
-                dist.all_reduce(self.importance)
+            parallel.allreduce_sum_(self.importance)     # CV loss is non-linear in the batch: the importance must be global (8e)
         bfs = self.bitfields()
         bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
         bg_arr = (ctypes.c_float * (3 * self.K))(*[float(x) for row in bg for x in row])
@@ -241,8 +240,7 @@ class Engine:
              self.importance if self.K > 1 else None, i32(1 if with_backward else 0), i32(march_slot), st)
 
     def adam_step(self, lr=None):
-        if self.world > 1:
-            dist.all_reduce(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
+        parallel.allreduce_sum_(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
         self.opt_step += 1
         call("rnb_engine_adam", self.flat, self.flat16, self.grads, self.exp_avg, self.exp_avg_sq, i64(self.n_params),
              f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), i64(self.opt_step),

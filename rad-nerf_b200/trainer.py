@@ -15,6 +15,7 @@ from __future__ import annotations
 import torch
 import torch.distributed as dist
 
+from . import parallel
 from . import synthetic as syn
 from .losses import NeRFLoss
 from .models.ml_rendering import ml_render
@@ -119,29 +120,18 @@ class Trainer:
             results = render(self.model, rays_o, rays_d, **kw)
         else:
             results = ml_render(self.model, self.gate, rays_o, rays_d, rays_d, **kw)
-            if self.world > 1:   # CV loss is non-linear in the batch: importance must be global (8e)
-                imp = results["gating_importance"]
-                tot = imp.detach().clone()
-                dist.all_reduce(tot)
-                results["gating_importance"] = imp + (tot - imp.detach())
+            results["gating_importance"] = parallel.global_importance(results["gating_importance"])   # 8e: CV loss is non-linear
         loss_d = self.loss_fn(results, {"rgb": target_rgb}, **self.lam)
-        if self.world > 1 and "cv_importance" in loss_d:
-            # the CV term is one GLOBAL scalar: its per-rank gradient pieces must be SUMMED, while the
-            # gradient all-reduce below averages -- pre-multiply by the world size
-            loss_d["cv_importance"] = loss_d["cv_importance"] * self.world
-        loss = sum(v.mean() for v in loss_d.values())
+        # every term is normalised by the GLOBAL element count: the gradient exchange is then a plain sum
+        loss = parallel.total_loss(loss_d, self.world)
         self.opt.zero_grad(set_to_none=True)
         (loss * self.loss_scale).backward()
-        if self.world > 1:
-            flat = torch.cat([p.grad.reshape(-1) for p in self.params])
-            dist.all_reduce(flat)          # one flat bucket over NCCL / NVLink
-            flat.mul_(1.0 / (self.world * self.loss_scale))
-            o = 0
-            for p in self.params:
-                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
-        else:
-            for p in self.params:
-                p.grad.mul_(1.0 / self.loss_scale)
+        flat = torch.cat([p.grad.reshape(-1) for p in self.params])
+        parallel.allreduce_sum_(flat)          # one flat bucket over NCCL / NVLink
+        flat.mul_(1.0 / self.loss_scale)
+        o = 0
+        for p in self.params:
+            p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
         self.opt.step()
         self.global_step += 1
         self.last_results = results
