@@ -141,6 +141,20 @@ int rnb_composite_test_fw(const float* sigmas, const float* rgbs, const float* d
                           rnb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
+ * (6) distortion loss -- replaces vren.distortion_loss_fw / distortion_loss_bw
+ *     (binding.cpp:197-231 -> losses.cu:9-175; caller losses.py:6-37).  ws, deltas, ts (N) f32; rays_a (n_rays,3) i64.
+ * ------------------------------------------------------------------------------------ */
+/* out: loss (n_rays) indexed by ray_idx (rays with no samples get 0); ws_inclusive_scan, wts_inclusive_scan (N):
+ * per-ray running sums of w and w*t.  Samples not covered by any ray are not written (the wrapper zero-fills). */
+int rnb_distortion_loss_fw(const float* ws, const float* deltas, const float* ts, const int64_t* rays_a,
+                           int64_t n_rays, int64_t N, float* loss, float* ws_inclusive_scan,
+                           float* wts_inclusive_scan, rnb_stream_t stream);
+/* dL_dloss (n_rays) indexed by ray_idx -> dL_dws (N). */
+int rnb_distortion_loss_bw(const float* dL_dloss, const float* ws_inclusive_scan, const float* wts_inclusive_scan,
+                           const float* ws, const float* deltas, const float* ts, const int64_t* rays_a,
+                           int64_t n_rays, int64_t N, float* dL_dws, rnb_stream_t stream);
+
+/* ------------------------------------------------------------------------------------
  * (3) multiresolution hash-grid encoding + SH4 -- replaces tinycudann's
  *     Encoding{Grid/Hash} and Encoding{SphericalHarmonics,4}
  *     (reference call sites: models/networks.py:42-55, 70-77, 234-256; tinycudann itself is

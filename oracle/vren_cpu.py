@@ -148,3 +148,48 @@ def composite_test_fw(sigmas, rgbs, deltas, ts, hits_t, alive, T_threshold, n_ef
     Ns = sigmas.shape[1]
     lib().orc_composite_test_fw(_p(sigmas), _p(rgbs), _p(deltas), _p(ts), _p(alive), ctypes.c_float(T_threshold),
                                 _p(n_eff), ctypes.c_int(Ns), ctypes.c_int64(A), _p(opacity), _p(depth), _p(rgb))
+
+
+def distortion_loss_fw(ws, deltas, ts, rays_a):
+    """losses.cu:9-60 (prefix_sums_kernel: serial thrust scans per ray), :92-93 (per-sample term as an ATen
+    expression: 2*(wts_incl*ws_excl - ws_incl*wts_excl) + ws*ws*deltas/3) and :44-60 (serial per-ray sum).
+    fp32, sequential accumulation like the reference's one-thread-per-ray loops."""
+    ws, deltas, ts = _f32(ws), _f32(deltas), _f32(ts)
+    rays_a = np.ascontiguousarray(rays_a, np.int64)
+    N = len(ws)
+    wts = (ws * ts).astype(np.float32)
+    wi = np.zeros(N, np.float32); we = np.zeros(N, np.float32); ti = np.zeros(N, np.float32); te = np.zeros(N, np.float32)
+    for _, s, n in rays_a:
+        if n <= 0:
+            continue
+        wi[s:s + n] = np.cumsum(ws[s:s + n], dtype=np.float32)
+        ti[s:s + n] = np.cumsum(wts[s:s + n], dtype=np.float32)
+        we[s + 1:s + n] = wi[s:s + n - 1]
+        te[s + 1:s + n] = ti[s:s + n - 1]
+    per = (np.float32(2) * (ti * we - wi * te) + np.float32(1.0 / 3) * ws * ws * deltas).astype(np.float32)
+    loss = np.zeros(len(rays_a), np.float32)
+    for r, s, n in rays_a:
+        acc = np.float32(0)
+        for k in range(s, s + n):
+            acc = np.float32(acc + per[k])
+        loss[r] = acc
+    return loss, wi, ti
+
+
+def distortion_loss_bw(dL_dloss, ws_inclusive_scan, wts_inclusive_scan, ws, deltas, ts, rays_a):
+    """losses.cu:113-136."""
+    g, wi, ti, ws, deltas, ts = (_f32(x) for x in (dL_dloss, ws_inclusive_scan, wts_inclusive_scan, ws, deltas, ts))
+    rays_a = np.ascontiguousarray(rays_a, np.int64)
+    out = np.zeros(len(ws), np.float32)
+    two3 = np.float32(2) / np.float32(3)
+    for r, s, n in rays_a:
+        if n <= 0:
+            continue
+        e = s + n - 1
+        ws_sum, wts_sum = wi[e], ti[e]
+        sl = slice(s, e + 1)
+        before = np.zeros(n, np.float32)
+        before[1:] = ts[s + 1:e + 1] * wi[s:e] - ti[s:e]
+        d = g[r] * np.float32(2) * (before + (wts_sum - ti[sl] - ts[sl] * (ws_sum - wi[sl])))
+        out[sl] = (d + g[r] * two3 * ws[sl] * deltas[sl]).astype(np.float32)
+    return out

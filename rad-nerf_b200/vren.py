@@ -185,10 +185,26 @@ def composite_test_fw(sigmas, rgbs, deltas, ts, hits_t, alive_indices, T_thresho
 
 
 def distortion_loss_fw(ws, deltas, ts, rays_a):
-    """binding.cpp:197-212 -- not on the Rad-NeRF hot path (unreachable from ml_render,
-    SURVEY.md 2.1 #7); out of scope this round."""
-    raise NotImplementedError("distortion_loss_fw is outside the hot path (SURVEY.md section 8f, f3)")
+    """binding.cpp:197-210 -> [loss (N_rays), ws_inclusive_scan (N), wts_inclusive_scan (N)]."""
+    for t, n in ((ws, "ws"), (deltas, "deltas"), (ts, "ts")):
+        check_input(t, n, torch.float32)
+    check_input(rays_a, "rays_a", torch.int64)
+    n_rays, N = rays_a.shape[0], ws.shape[0]
+    loss = torch.zeros(n_rays, device=ws.device)
+    wsi = torch.zeros(N, device=ws.device)
+    wtsi = torch.zeros(N, device=ws.device)
+    call("rnb_distortion_loss_fw", ws, deltas, ts, rays_a, i64(n_rays), i64(N), loss, wsi, wtsi, stream_arg(ws.device))
+    return [loss, wsi, wtsi]
 
 
 def distortion_loss_bw(dL_dloss, ws_inclusive_scan, wts_inclusive_scan, ws, deltas, ts, rays_a):
-    raise NotImplementedError("distortion_loss_bw is outside the hot path (SURVEY.md section 8f, f3)")
+    """binding.cpp:212-231 -> dL_dws (N)."""
+    for t, n in ((dL_dloss, "dL_dloss"), (ws_inclusive_scan, "ws_inclusive_scan"), (wts_inclusive_scan, "wts_inclusive_scan"),
+                 (ws, "ws"), (deltas, "deltas"), (ts, "ts")):
+        check_input(t, n, torch.float32)
+    check_input(rays_a, "rays_a", torch.int64)
+    n_rays, N = rays_a.shape[0], ws.shape[0]
+    dL_dws = torch.zeros(N, device=ws.device)
+    call("rnb_distortion_loss_bw", dL_dloss, ws_inclusive_scan, wts_inclusive_scan, ws, deltas, ts, rays_a, i64(n_rays), i64(N),
+         dL_dws, stream_arg(ws.device))
+    return dL_dws

@@ -107,3 +107,57 @@ def test_product_matches_reference_golden(cfg):
                                      dl, ts, ra, op, dp, col, 1e-4)
     assert np.abs(gc.cpu().numpy() - g["bw_drgbs"]).max() < 1e-6
     assert np.abs(gs.cpu().numpy() - g["bw_dsigmas"]).max() < 1e-4 * max(1.0, np.abs(g["bw_dsigmas"]).max())
+
+
+# ---- distortion loss (vren.distortion_loss_fw / _bw; tests/golden/make_golden_distortion.py) -------------------------
+# fp32 sums: the reference accumulates serially per ray, the warp kernels by tree -> 1e-5 relative to the ray's scale.
+def _load_distortion():
+    p = os.path.join(GOLDEN, "distortion.npz")
+    if not os.path.exists(p):
+        pytest.skip("golden fixture missing")
+    return np.load(p)
+
+
+def _close(a, b, tol=2e-5):
+    scale = max(1.0, float(np.abs(b).max()))
+    return float(np.abs(a - b).max()) <= tol * scale
+
+
+def test_oracle_distortion_matches_reference_golden():
+    g = _load_distortion()
+    loss, wi, ti = O.distortion_loss_fw(g["ws"], g["deltas"], g["ts"], g["rays_a"])
+    assert _close(wi, g["ws_inclusive_scan"]) and _close(ti, g["wts_inclusive_scan"])
+    assert _close(loss, g["loss"])
+    dws = O.distortion_loss_bw(g["dL_dloss"], g["ws_inclusive_scan"], g["wts_inclusive_scan"], g["ws"], g["deltas"], g["ts"], g["rays_a"])
+    assert _close(dws, g["dL_dws"])
+
+
+@pytest.mark.gpu
+def test_product_distortion_matches_reference_golden():
+    import torch
+    from radnerf_b200 import vren
+    from radnerf_b200.losses import DistortionLoss
+    g = _load_distortion()
+    cu = lambda k: torch.from_numpy(g[k]).cuda()
+    loss, wi, ti = vren.distortion_loss_fw(cu("ws"), cu("deltas"), cu("ts"), cu("rays_a"))
+    assert _close(wi.cpu().numpy(), g["ws_inclusive_scan"]) and _close(ti.cpu().numpy(), g["wts_inclusive_scan"])
+    assert _close(loss.cpu().numpy(), g["loss"])
+    dws = vren.distortion_loss_bw(cu("dL_dloss"), cu("ws_inclusive_scan"), cu("wts_inclusive_scan"), cu("ws"), cu("deltas"), cu("ts"), cu("rays_a"))
+    assert _close(dws.cpu().numpy(), g["dL_dws"])
+    # autograd surface (losses.py:6-37): gradient of sum(loss * dL) w.r.t. ws equals the analytic backward
+    ws = cu("ws").requires_grad_(True)
+    out = DistortionLoss.apply(ws, cu("deltas"), cu("ts"), cu("rays_a"))
+    (out * cu("dL_dloss")).sum().backward()
+    assert _close(ws.grad.cpu().numpy(), g["dL_dws"])
+    # and it is the true derivative: central differences on a few samples, in float64 through the oracle
+    w64 = g["ws"].astype(np.float64)
+    for k in (0, 100, 2500, 7000):
+        e = np.zeros_like(w64); e[k] = 1e-3
+        lp, _, _ = O.distortion_loss_fw(w64 + e, g["deltas"], g["ts"], g["rays_a"])
+        lm, _, _ = O.distortion_loss_fw(w64 - e, g["deltas"], g["ts"], g["rays_a"])
+        fd = float(((lp - lm) * g["dL_dloss"]).sum() / 2e-3)
+        assert abs(fd - float(g["dL_dws"][k])) < 5e-2 * max(1e-3, abs(fd))
+    # empty input
+    z = torch.zeros(0, device="cuda"); ra = torch.zeros(0, 3, dtype=torch.int64, device="cuda")
+    l0, _, _ = vren.distortion_loss_fw(z, z, z, ra)
+    assert l0.numel() == 0
