@@ -325,7 +325,18 @@ def run_product(args):
             roof = {"kernel": top, "bound": "tensor", "achieved": ff, "peak": tflops, "unit": "TFLOP/s", "frac": ff / tflops}
         else:
             roof = {"kernel": top, "bound": "hbm", "achieved": fb, "peak": hbm, "unit": "GB/s", "frac": fb / hbm}
-        roof.update({"traffic": None, "peak_source": which, "hbm_frac": fb / hbm, "tensor_frac": ff / tflops,
+        # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/, same workload and batch)
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["kernels"]
+            kname = {"field_bwd": "field_bwd_tc_kernel", "field_fwd": "field_fwd_tc_kernel<1>", "march": "eng_march_kernel<1>",
+                     "adam": "eng_adam_kernel"}.get(top)
+            if kname in tj and args.workload == "radnerf_tat_k2" and tr.engine is not None:
+                traffic = tj[kname]["dram_bytes_per_launch"]
+        except (OSError, KeyError, ValueError):
+            pass
+        roof.update({"traffic": traffic, "traffic_unit": "bytes/launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
+                     "algorithmic_bytes_per_launch": STAGE_BYTES.get(top, lambda *a: 0)(N, KR, Pn), "peak_source": which, "hbm_frac": fb / hbm, "tensor_frac": ff / tflops,
                      "launch_ms": t_ms, "share_of_step": t_ms * stage_ms[top][1] / args.steps / ms_step,
                      "stage_ms_per_launch": {k: round(v[0], 4) for k, v in stage_ms.items()},
                      "stages_share_of_step": sum(v[0] * v[1] for v in stage_ms.values()) / args.steps / ms_step})
