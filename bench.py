@@ -182,7 +182,9 @@ def run_product(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        opts = dist.ProcessGroupNCCL.Options()
+        opts.is_high_priority_stream = True      # the step's two small collectives must not queue behind side-stream work
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
     syn, w = workload(args.workload)
     from radnerf_b200 import _lib
     from radnerf_b200.trainer import Trainer

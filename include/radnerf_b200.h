@@ -400,6 +400,35 @@ int rnb_grid_update(const rnb_engine_config* cfg, void* workspace, const void* p
                     uint8_t* const* bitfields, int warmup, float decay, float density_threshold, const float* noise,
                     const int32_t* coords1, const float* pick_u, uint64_t seed, int workspace_is_fresh, rnb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * (multi-GPU) The gradient exchange and the optimizer as ONE kernel over NVLink peer memory: rank r owns shard r of
+ *     the flat parameter vector; its kernel sums that shard of every rank's gradient buffer with peer loads (fixed
+ *     order), applies Adam to its fp32 master / moments, and stores the fp16 compute copy of the shard into every
+ *     rank's parameter buffer (reduce-scatter + Adam + all-gather; replaces DDP's NCCL all-reduce followed by a
+ *     replicated FusedAdam, train_ml.py:143, 309-318).  The caller brackets it with two small collectives (every rank's
+ *     backward done before; every rank's kernel done before parameters are read or gradients re-zeroed) and zeroes its
+ *     own gradient buffer afterwards.  fp32 master parameters and moments outside a rank's own shard are NOT kept
+ *     current (gather them when a checkpoint is written).
+ * ------------------------------------------------------------------------------------ */
+#define RNB_MAX_PEERS 8
+/* cudaMalloc + zero-fill + CUDA IPC handle (64 bytes) for a buffer that other processes of this node map */
+int rnb_peer_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64);
+int rnb_peer_open(const void* ipc_handle_64, void** dev_ptr);      /* map a peer's allocation (enables peer access lazily) */
+int rnb_peer_close(void* dev_ptr);
+int rnb_peer_free(void* dev_ptr);
+int rnb_adam_shard_bounds(int64_t n, int rank, int world, int64_t* lo, int64_t* hi);
+/* grads_peers[p], params_f16_peers[p]: rank p's gradient / fp16 parameter buffer as mapped in THIS process
+ * ([rank] = the local ones); params_f32, exp_avg, exp_avg_sq: local, full length n (only the shard is touched). */
+/* Parameters [0, n_sharded) are sharded over the ranks; [n_sharded, n) -- the gate network, last block of the flat
+ * vector -- is updated redundantly by every rank from the same reduced gradient, so that the next step's gate forward and
+ * its importance all-reduce (which then doubles as the "every rank's kernel is done" barrier) need no remote parameters.
+ * zero_grads (may be NULL): this rank's gradient buffer of the PREVIOUS step (n floats), cleared by the same kernel;
+ * with two alternating gradient buffers no separate zero-fill pass and no second barrier are needed. */
+int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers,
+                            float* params_f32, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded,
+                            float* zero_grads, float lr, float beta1, float beta2, float eps, int64_t step,
+                            float grad_scale, rnb_stream_t stream);
+
 /* Optional per-stage device timing of the fused step (CUDA events around every stage; off by default).
  * Stage order: gate, march, scan, expand, field_fwd, composite_fw, blend_loss, composite_bw, field_bwd,
  * gate_bwd, adam.  rnb_engine_profile_read synchronises, returns the accumulated milliseconds and call

@@ -1,0 +1,170 @@
+// peer.cu -- the data-parallel exchange of the training step as ONE kernel over NVLink peer memory.
+//
+// The reference's multi-GPU step is DDP: bucketed NCCL all-reduce of every gradient, then the same Adam step on every
+// rank (train_ml.py:143, 309-318).  Here rank r OWNS shard r of the flat parameter vector.  After the backward pass,
+// one kernel per rank does, for its shard only,
+//     g   = sum over ranks p = 0..W-1 of grads_p[shard]      (plain peer loads over NVLink, fixed order: the same bits
+//                                                             on every run and independent of the reading rank)
+//     Adam on the fp32 master / moments of the shard          (local, 1/W of the optimizer work)
+//     fp16 compute copy of the shard -> ALL ranks' buffers    (peer stores)
+// i.e. reduce-scatter + optimizer + all-gather with no staging buffer and half the all-gather payload (fp16, 2 B per
+// parameter instead of the 4 B an all-reduce returns).  Ordering between ranks comes from the two small collectives the
+// host side issues around it (parallel.py): every rank's backward precedes the kernel, and nobody reads parameters or
+// re-zeroes gradients before every rank's kernel is done.  The kernel itself never waits on another GPU.
+//
+// Buffers that peers touch (gradients: read; fp16 parameters: written) are allocated with rnb_peer_alloc (cudaMalloc +
+// CUDA IPC handle) and mapped into the other processes with rnb_peer_open.
+#include <string.h>
+
+#include "common.cuh"
+
+namespace rnb {
+
+struct PeerPtrs {
+  const float* grads[RNB_MAX_PEERS];
+  __half* p16[RNB_MAX_PEERS];
+};
+
+template <int W>
+__device__ __forceinline__ float4 sum_peers(const PeerPtrs& P, int world, int64_t i4) {
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 g[W];
+#pragma unroll
+  for (int p = 0; p < W; p++)
+    if (p < world) g[p] = __ldcs(reinterpret_cast<const float4*>(P.grads[p]) + i4);   // all loads in flight before the first add
+#pragma unroll
+  for (int p = 0; p < W; p++)
+    if (p < world) { acc.x += g[p].x; acc.y += g[p].y; acc.z += g[p].z; acc.w += g[p].w; }
+  return acc;
+}
+
+__device__ __forceinline__ float4 adam4(float4 gg, float* __restrict__ p32, float* __restrict__ m, float* __restrict__ v, int64_t i,
+                                        float step_size, float beta1, float beta2, float eps, float inv_sqrt_bc2, float grad_scale) {
+  float4 pp = reinterpret_cast<float4*>(p32)[i], mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+  float* Pp = &pp.x; float* G = &gg.x; float* M = &mm.x; float* V = &vv.x;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const float gr = G[k] * grad_scale;
+    M[k] = beta1 * M[k] + (1.f - beta1) * gr;
+    V[k] = beta2 * V[k] + (1.f - beta2) * gr * gr;
+    Pp[k] -= step_size * M[k] / (sqrtf(V[k]) * inv_sqrt_bc2 + eps);
+  }
+  reinterpret_cast<float4*>(p32)[i] = pp; reinterpret_cast<float4*>(m)[i] = mm; reinterpret_cast<float4*>(v)[i] = vv;
+  return pp;
+}
+__device__ __forceinline__ uint2 to_half4(float4 pp) {
+  const __half2 a = __floats2half2_rn(pp.x, pp.y), b = __floats2half2_rn(pp.z, pp.w);
+  return make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+template <int W>
+__device__ __forceinline__ float4 sum_all(const PeerPtrs& P, int world, int64_t i) {
+  return sum_peers<W>(P, world, i);
+}
+__device__ __forceinline__ float4 sum_any(const PeerPtrs& P, int world, int64_t i) {
+  return world <= 2 ? sum_peers<2>(P, world, i) : world <= 4 ? sum_peers<4>(P, world, i) : sum_peers<RNB_MAX_PEERS>(P, world, i);
+}
+
+// All indices in units of 4 parameters.
+//   [lo4, hi4)      this rank's shard: reduce over ranks, Adam, fp16 result to EVERY rank
+//   [rep_lo4, rep_hi4)  replicated block (the gate network): every rank reduces and updates its own replica, so that the
+//                   next gate forward needs no remote data
+//   zero_buf[0, zero_n4)  the local gradient buffer of the PREVIOUS step (all peers finished reading it before this
+//                   kernel was allowed to start): cleared here for the next step
+__global__ void __launch_bounds__(256) adam_sharded_kernel(PeerPtrs P, int world, int rank, float* __restrict__ p32, float* __restrict__ m,
+                                                           float* __restrict__ v, int64_t lo4, int64_t hi4, int64_t rep_lo4, int64_t rep_hi4,
+                                                           float* __restrict__ zero_buf, int64_t zero_n4, float step_size, float beta1,
+                                                           float beta2, float eps, float inv_sqrt_bc2, float grad_scale) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (int64_t i = lo4 + t0; i < hi4; i += stride) {
+    const float4 pp = adam4(sum_any(P, world, i), p32, m, v, i, step_size, beta1, beta2, eps, inv_sqrt_bc2, grad_scale);
+    const uint2 q = to_half4(pp);
+#pragma unroll
+    for (int p = 0; p < RNB_MAX_PEERS; p++)
+      if (p < world) reinterpret_cast<uint2*>(P.p16[p])[i] = q;
+  }
+  for (int64_t i = rep_lo4 + t0; i < rep_hi4; i += stride) {
+    const float4 pp = adam4(sum_any(P, world, i), p32, m, v, i, step_size, beta1, beta2, eps, inv_sqrt_bc2, grad_scale);
+    reinterpret_cast<uint2*>(P.p16[rank])[i] = to_half4(pp);
+  }
+  if (zero_buf != nullptr)
+    for (int64_t i = t0; i < zero_n4; i += stride) reinterpret_cast<float4*>(zero_buf)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+}  // namespace rnb
+
+using namespace rnb;
+
+extern "C" {
+
+int rnb_peer_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle_64) {
+  const char* what = "rnb_peer_alloc";
+  RNB_REQUIRE(bytes > 0 && dev_ptr && ipc_handle_64, what);
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  RNB_CUDA(cudaMalloc(&p, (size_t)bytes), what);
+  RNB_CUDA(cudaMemset(p, 0, (size_t)bytes), what);
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) { cudaFree(p); RNB_CUDA(e, what); }
+  memcpy(ipc_handle_64, &h, 64);
+  *dev_ptr = p;
+  return RNB_OK;
+}
+
+int rnb_peer_open(const void* ipc_handle_64, void** dev_ptr) {
+  const char* what = "rnb_peer_open";
+  RNB_REQUIRE(ipc_handle_64 && dev_ptr, what);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle_64, 64);
+  RNB_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess), what);
+  return RNB_OK;
+}
+
+int rnb_peer_close(void* dev_ptr) {
+  RNB_CUDA(cudaIpcCloseMemHandle(dev_ptr), "rnb_peer_close");
+  return RNB_OK;
+}
+
+int rnb_peer_free(void* dev_ptr) {
+  RNB_CUDA(cudaFree(dev_ptr), "rnb_peer_free");
+  return RNB_OK;
+}
+
+/* this rank's shard [lo, hi) of n parameters split over `world` ranks in multiples of 4 */
+int rnb_adam_shard_bounds(int64_t n, int rank, int world, int64_t* lo, int64_t* hi) {
+  const char* what = "rnb_adam_shard_bounds";
+  RNB_REQUIRE(n > 0 && n % 4 == 0 && world >= 1 && rank >= 0 && rank < world && lo && hi, what);
+  const int64_t n4 = n / 4, per = (n4 + world - 1) / world;
+  const int64_t a = per * rank < n4 ? per * rank : n4, b = per * (rank + 1) < n4 ? per * (rank + 1) : n4;
+  *lo = a * 4; *hi = b * 4;
+  return RNB_OK;
+}
+
+int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers, float* params_f32,
+                            float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded, float* zero_grads, float lr, float beta1,
+                            float beta2, float eps, int64_t step, float grad_scale, rnb_stream_t stream) {
+  const char* what = "rnb_engine_adam_sharded";
+  RNB_REQUIRE(world >= 1 && world <= RNB_MAX_PEERS && rank >= 0 && rank < world && grads_peers && params_f16_peers, what);
+  RNB_REQUIRE(params_f32 && exp_avg && exp_avg_sq && n > 0 && n % 4 == 0 && step >= 1, what);
+  RNB_REQUIRE(n_sharded > 0 && n_sharded <= n && n_sharded % 4 == 0 && ((uintptr_t)zero_grads & 15) == 0, what);
+  PeerPtrs P;
+  for (int p = 0; p < RNB_MAX_PEERS; p++) { P.grads[p] = nullptr; P.p16[p] = nullptr; }
+  for (int p = 0; p < world; p++) {
+    RNB_REQUIRE(grads_peers[p] && params_f16_peers[p], what);
+    RNB_REQUIRE(((uintptr_t)grads_peers[p] & 15) == 0 && ((uintptr_t)params_f16_peers[p] & 7) == 0, what);
+    P.grads[p] = grads_peers[p]; P.p16[p] = (__half*)params_f16_peers[p];
+  }
+  int64_t lo, hi;
+  if (int rc = rnb_adam_shard_bounds(n_sharded, rank, world, &lo, &hi)) return rc;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+  const float step_size = (float)(lr / bc1), inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  int64_t blocks = ((zero_grads ? n : hi - lo) / 4 + 255) / 256;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks < 1) blocks = 1;
+  adam_sharded_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(P, world, rank, params_f32, exp_avg, exp_avg_sq, lo / 4, hi / 4, n_sharded / 4,
+                                                                 n / 4, zero_grads, n / 4, step_size, beta1, beta2, eps, inv_sqrt_bc2, grad_scale);
+  return check_launch(what);
+}
+
+}  // extern "C"

@@ -63,7 +63,7 @@ class _GridLayout(ctypes.Structure):
 class Engine:
     def __init__(self, model, gate=None, n_rays=8192, exp_step_factor=0.0, samples_per_ray=128, max_samples=1024,
                  T_threshold=1e-4, near_distance=0.01, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
-                 loss_scale=128.0 * 1024.0, lr=1e-2, betas=(0.9, 0.999), eps=1e-15):
+                 loss_scale=128.0 * 1024.0, lr=1e-2, betas=(0.9, 0.999), eps=1e-15, sharded_optimizer=True):
         _lib.lib()
         self.model, self.gate = model, gate
         self.K = K = getattr(model, "size", 1)
@@ -86,8 +86,19 @@ class Engine:
         self.n_params = off
         self.offsets = offs
         self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
-        self.flat16 = torch.zeros(off, dtype=torch.float16, device=dev)
-        self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.world = parallel.world_size()
+        self.sharded = self.world > 1 and sharded_optimizer
+        if self.sharded:
+            # buffers the other ranks address over NVLink (csrc/peer.cu): gradients are read, fp16 parameters written
+            # (two alternating gradient buffers: the one peers read in step n is cleared by this rank's kernel of step n+1)
+            self._peer_g = [parallel.PeerBuffer(off * 4, dev), parallel.PeerBuffer(off * 4, dev)]
+            self._peer_p = parallel.PeerBuffer(off * 2, dev)
+            self._g = 0
+            self.grads = self._peer_g[0].local.view(torch.float32)
+            self.flat16 = self._peer_p.local.view(torch.float16)
+        else:
+            self.flat16 = torch.zeros(off, dtype=torch.float16, device=dev)
+            self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
         self.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
         self._mods = mods
@@ -134,7 +145,6 @@ class Engine:
         self.loss = v("loss", torch.float32, (8,))
         self.lr, self.betas, self.eps = lr, betas, eps
         self.opt_step = 0
-        self.world = parallel.world_size()
         # marching ahead (rnb_engine_march): the next batch's samples are produced on a side stream into the other slot
         self._march_stream = None
         self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
@@ -183,8 +193,9 @@ class Engine:
             noise = torch.rand(self.K, self.n_rays, device=self.device)
         if self._march_stream is None:
             self._march_stream = torch.cuda.Stream(self.device)
-        # the batch about to be trained sits in the slot of its own prefetch, or will be marched inline into slot 0
-        busy = next(iter(self._ahead.values()))[0] if self._ahead else 0
+        # the batch being (or about to be) trained sits in the slot of its own prefetch if that is still pending, else in
+        # self._slot (forward_backward has already claimed it)
+        busy = next(iter(self._ahead.values()))[0] if self._ahead else self._slot
         slot = busy ^ 1
         cur = torch.cuda.current_stream(self.device)
         ready = torch.cuda.Event()
@@ -199,9 +210,11 @@ class Engine:
             done.record(self._march_stream)
         self._ahead[(rays_o.data_ptr(), rays_d.data_ptr())] = (slot, rays_o, rays_d, noise, done)
 
-    def forward_backward(self, rays_o, rays_d, target_rgb, noise, bg, with_backward=True):
+    def forward_backward(self, rays_o, rays_d, target_rgb, noise, bg, with_backward=True, next_rays=None):
         """noise (K,R) f32 in [0,1); bg: K x 3 python floats.  Fills the result views and, with
-        `with_backward`, accumulates into self.grads.  Returns nothing; no host synchronisation."""
+        `with_backward`, accumulates into self.grads.  Returns nothing; no host synchronisation.
+        next_rays = (rays_o, rays_d) of the following batch: marched ahead on the side stream (prefetch), issued after
+        the gate's importance all-reduce so that the small collective does not queue behind 2048 marching CTAs."""
         c = self.cfg
         for t, n in ((rays_o, "rays_o"), (rays_d, "rays_d"), (target_rgb, "target_rgb")):
             _lib.check_input(t, n, torch.float32)
@@ -229,6 +242,8 @@ class Engine:
         if self.K > 1:
             call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
             parallel.allreduce_sum_(self.importance)     # CV loss is non-linear in the batch: the importance must be global (8e)
+        if next_rays is not None:
+            self.prefetch(next_rays[0], next_rays[1])
         bfs = self.bitfields()
         bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
         bg_arr = (ctypes.c_float * (3 * self.K))(*[float(x) for row in bg for x in row])
@@ -240,11 +255,46 @@ class Engine:
              self.importance if self.K > 1 else None, i32(1 if with_backward else 0), i32(march_slot), st)
 
     def adam_step(self, lr=None):
-        parallel.allreduce_sum_(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
         self.opt_step += 1
+        if self.sharded:
+            # one kernel: this rank's shard of sum_p grads_p (peer loads) -> Adam -> fp16 parameters into every rank's buffer
+            # (peer stores); the gate block is updated redundantly on every rank; the previous step's gradient buffer is
+            # cleared.  The stream barrier in front orders it after every rank's backward.  Behind it, the next step's gate
+            # forward touches only this rank's own gate replica and the importance all-reduce that follows it completes only
+            # once every rank has left this kernel -- for K = 1 there is no such all-reduce, so a second barrier is issued.
+            parallel.stream_barrier(self.device)
+            cur, prev = self._peer_g[self._g], self._peer_g[self._g ^ 1]
+            n_sharded = self.offsets["gate"] if self.K > 1 else self.n_params
+            call("rnb_engine_adam_sharded", i32(parallel.rank()), i32(self.world), cur.pointer_array(),
+                 self._peer_p.pointer_array(), self.flat, self.exp_avg, self.exp_avg_sq, i64(self.n_params), i64(n_sharded),
+                 prev.local, f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps),
+                 i64(self.opt_step), f32(1.0), stream_arg(self.device))
+            if self.K == 1:
+                parallel.stream_barrier(self.device)
+            self._g ^= 1
+            self.grads = self._peer_g[self._g].local.view(torch.float32)      # (cleared by the kernel of the previous step)
+            self._master_stale = True
+            return
+        parallel.allreduce_sum_(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
         call("rnb_engine_adam", self.flat, self.flat16, self.grads, self.exp_avg, self.exp_avg_sq, i64(self.n_params),
              f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), i64(self.opt_step),
              f32(1.0), stream_arg(self.device))
+
+    def gather_master(self):
+        """Sharded optimizer: fp32 master parameters and Adam moments are current only inside each rank's own shard.
+        Gathers them (for a checkpoint, or before using the Python operator surface on these modules)."""
+        if not self.sharded or not getattr(self, "_master_stale", False):
+            return
+        n_sh = self.offsets["gate"] if self.K > 1 else self.n_params      # the gate block is replicated (and current) everywhere
+        sl = parallel.adam_shard(n_sh)
+        for t in (self.flat, self.exp_avg, self.exp_avg_sq):
+            own, rep = t[sl].clone(), t[n_sh:].clone()
+            t.zero_()
+            t[sl] = own
+            if parallel.rank() == 0:
+                t[n_sh:] = rep
+            parallel.allreduce_sum_(t)
+        self._master_stale = False
 
     def background(self, random_bg=False):
         if self.exp_step_factor == 0:
@@ -253,9 +303,9 @@ class Engine:
             return torch.rand(self.K, 3).tolist()
         return [[0.0, 0.0, 0.0]] * self.K
 
-    def step(self, rays_o, rays_d, target_rgb, lr=None, random_bg=False, noise=None):
+    def step(self, rays_o, rays_d, target_rgb, lr=None, random_bg=False, noise=None, next_rays=None):
         """One training step.  Returns the loss vector view [total, rgb, opacity, cv, depth_mutual, ...] (device)."""
-        self.forward_backward(rays_o, rays_d, target_rgb, noise, self.background(random_bg), True)
+        self.forward_backward(rays_o, rays_d, target_rgb, noise, self.background(random_bg), True, next_rays)
         self.adam_step(lr)
         return self.loss
 

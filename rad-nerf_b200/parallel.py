@@ -93,3 +93,71 @@ def gather_frame(local: torch.Tensor, H: int, W: int) -> torch.Tensor:
         rows = torch.arange(r, H, world)
         out[rows] = parts[r][:len(rows)]
     return out.reshape(H * W, C)
+
+
+# ---- peer memory (NVLink) for the fused reduce-scatter + Adam + all-gather kernel (csrc/peer.cu) -----------------------
+class _RawCuda:
+    """Exposes a raw device allocation through __cuda_array_interface__ so that torch can view it."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerBuffer:
+    """A device buffer of `nbytes` that every rank of the node can address: allocated here with rnb_peer_alloc, its CUDA
+    IPC handle exchanged over torch.distributed, the peers' allocations mapped with rnb_peer_open.
+    .local: uint8 torch view of this rank's allocation; .ptrs: this buffer on every rank, as mapped in this process."""
+
+    def __init__(self, nbytes, device):
+        import ctypes
+        from . import _lib
+        self._lib = _lib
+        lib = _lib.lib()
+        ptr = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        _lib.call("rnb_peer_alloc", ctypes.c_int64(nbytes), ctypes.byref(ptr), handle)
+        self.ptr = ptr.value
+        self.local = torch.as_tensor(_RawCuda(self.ptr, nbytes), device=device)
+        world, rk = world_size(), rank()
+        handles = [None] * world
+        dist.all_gather_object(handles, bytes(handle))
+        self.ptrs = []
+        self._opened = []
+        for r in range(world):
+            if r == rk:
+                self.ptrs.append(self.ptr)
+                continue
+            q = ctypes.c_void_p()
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
+            _lib.call("rnb_peer_open", buf, ctypes.byref(q))
+            self.ptrs.append(q.value)
+            self._opened.append(q.value)
+        del lib
+
+    def pointer_array(self):
+        import ctypes
+        return (ctypes.c_void_p * len(self.ptrs))(*self.ptrs)
+
+
+def adam_shard(n: int, rk: int | None = None, world: int | None = None) -> slice:
+    """Slice of the flat parameter vector a rank owns in the sharded optimizer (multiples of 4 parameters; mirrors
+    rnb_adam_shard_bounds)."""
+    rk = rank() if rk is None else rk
+    world = world_size() if world is None else world
+    n4 = n // 4
+    per = (n4 + world - 1) // world
+    return slice(min(per * rk, n4) * 4, min(per * (rk + 1), n4) * 4)
+
+
+_token = {}
+
+
+def stream_barrier(device) -> None:
+    """A collective that orders the ranks' CURRENT STREAMS without blocking the host: everything enqueued before it on
+    every rank completes before anything enqueued after it on any rank starts."""
+    if world_size() == 1:
+        return
+    t = _token.get(device)
+    if t is None:
+        t = _token[device] = torch.zeros(1, device=device)
+    dist.all_reduce(t)

@@ -106,10 +106,10 @@ class Trainer:
         occupancy update, so that every batch is marched against the same bitfields as in the sequential order."""
         if self.global_step % self.update_interval == 0:
             self._grid_update()
-        if self.engine is not None and next_rays is not None and (self.global_step + 1) % self.update_interval != 0:
-            self.engine.prefetch(next_rays[0], next_rays[1])
         if self.engine is not None:
-            loss = self.engine.step(rays_o, rays_d, target_rgb, lr=self.lr, random_bg=self.random_bg)
+            if next_rays is not None and (self.global_step + 1) % self.update_interval == 0:
+                next_rays = None
+            loss = self.engine.step(rays_o, rays_d, target_rgb, lr=self.lr, random_bg=self.random_bg, next_rays=next_rays)
             self.global_step += 1
             self.last_results = self.engine.results()
             return loss[0]
