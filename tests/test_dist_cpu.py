@@ -100,3 +100,22 @@ def test_single_process_helpers_are_identity():
     terms = {"rgb": torch.ones(8, 3) * 2.0, "cv": torch.tensor(0.5)}
     assert abs(float(parallel.total_loss(terms)) - 2.5) < 1e-6
     assert abs(float(parallel.reported_loss(terms)) - 2.5) < 1e-6
+
+
+def test_adam_shards_tile_the_parameter_vector():
+    """parallel.adam_shard mirrors rnb_adam_shard_bounds (csrc/peer.cu): shards are multiples of 4 parameters, disjoint,
+    ordered, and cover [0, n) for every world size -- checked against the C function through the C ABI (no GPU needed)."""
+    import ctypes
+    from radnerf_b200 import _lib
+    lib = _lib.lib()
+    for n in (8, 11_400_000, 4 * 7 + 4, 1024):
+        for world in (1, 2, 3, 4, 8):
+            end = 0
+            for r in range(world):
+                sl = parallel.adam_shard(n, r, world)
+                lo, hi = ctypes.c_int64(), ctypes.c_int64()
+                assert lib.rnb_adam_shard_bounds(ctypes.c_int64(n), r, world, ctypes.byref(lo), ctypes.byref(hi)) == 0
+                assert (sl.start, sl.stop) == (lo.value, hi.value)
+                assert sl.start == end and sl.start % 4 == 0 and sl.stop >= sl.start
+                end = sl.stop
+            assert end == n
