@@ -43,19 +43,34 @@ __device__ __forceinline__ uint32_t pack2h(float a, float b) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-// one level of the multiresolution grid -> packed half2 (same arithmetic as hashgrid_fwd_kernel)
+// one level of the multiresolution grid -> packed half2 (same arithmetic as hashgrid_fwd_kernel).
+// Corners 2p and 2p+1 are x-neighbours.  On dense levels their entries are adjacent; on hashed levels
+// idx = x ^ (y*P1) ^ (z*P2), so for even x the neighbour is idx ^ 1.  Either way, half of the time both live in one
+// aligned 8-byte pair: the pair is fetched with one load and the second 4-byte gather is issued only by the lanes that
+// still need it (fewer L1 tag lookups and sectors -- the unit this kernel is bound by).
 __device__ __forceinline__ uint32_t tc_encode_level(const TcFieldArgs& A, int l, float x, float y, float z) {
   const uint32_t off = A.g.offset[l];
   const LevelCorners L = level_corners(x, y, z, A.g.scale[l], A.g.res[l], A.g.offset[l + 1] - off);
-  const __half2* t = A.table + off;
-  __half2 v[8];
+  const __half2* t = A.table + off;                      // level offsets are multiples of 8 entries: pairs stay aligned
+  uint2 pr[4];
+  uint32_t vb[4];
 #pragma unroll
-  for (int k = 0; k < 8; k++) v[k] = __ldg(t + L.idx[k]);
+  for (int p = 0; p < 4; p++) pr[p] = __ldg(reinterpret_cast<const uint2*>(t) + (L.idx[2 * p] >> 1));
+#pragma unroll
+  for (int p = 0; p < 4; p++) {
+    vb[p] = 0u;
+    if ((L.idx[2 * p] ^ L.idx[2 * p + 1]) != 1u) vb[p] = *reinterpret_cast<const uint32_t*>(t + L.idx[2 * p + 1]);
+  }
   float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-  for (int k = 0; k < 8; k++) {
-    const float2 f = __half22float2(v[k]);
-    a0 = fmaf(L.w[k], f.x, a0); a1 = fmaf(L.w[k], f.y, a1);
+  for (int p = 0; p < 4; p++) {
+    const bool odd = L.idx[2 * p] & 1u;
+    const uint32_t ea = odd ? pr[p].y : pr[p].x;
+    const uint32_t eb = ((L.idx[2 * p] ^ L.idx[2 * p + 1]) == 1u) ? (odd ? pr[p].x : pr[p].y) : vb[p];
+    const float2 fa = __half22float2(*reinterpret_cast<const __half2*>(&ea));
+    const float2 fb = __half22float2(*reinterpret_cast<const __half2*>(&eb));
+    a0 = fmaf(L.w[2 * p], fa.x, a0); a1 = fmaf(L.w[2 * p], fa.y, a1);
+    a0 = fmaf(L.w[2 * p + 1], fb.x, a0); a1 = fmaf(L.w[2 * p + 1], fb.y, a1);
   }
   return pack2h(a0, a1);
 }
@@ -179,16 +194,28 @@ __global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __re
     }
     tc::fence_async_smem();
     __syncthreads();
-    for (int64_t tile = (int64_t)blockIdx.x * kWG + wg; tile < n_tiles; tile += (int64_t)gridDim.x * kWG) {
+    // The sample -> ray -> origin/direction lookups are two dependent global loads in front of the first gather: they are
+    // issued one tile ahead (while this tile is in its layer chain) and carried in registers.
+    const int64_t tile0 = (int64_t)blockIdx.x * kWG + wg, tstride = (int64_t)gridDim.x * kWG;
+    float nt = 0.f, nox = 0.f, noy = 0.f, noz = 0.f, ndx = 0.f, ndy = 0.f, ndz = 0.f;
+    if (tile0 < n_tiles && base + tile0 * kRows + row < pass_end) {
+      const int64_t s0 = base + tile0 * kRows + row;
+      const int r = __ldg(A.ray_id + s0);
+      nt = __ldg(A.ts + s0);
+      nox = __ldg(A.rays_o + 3 * r); noy = __ldg(A.rays_o + 3 * r + 1); noz = __ldg(A.rays_o + 3 * r + 2);
+      ndx = __ldg(A.rays_d + 3 * r); ndy = __ldg(A.rays_d + 3 * r + 1); ndz = __ldg(A.rays_d + 3 * r + 2);
+    }
+    for (int64_t tile = tile0; tile < n_tiles; tile += tstride) {
       const int64_t s = base + tile * kRows + row;
       const bool valid = s < pass_end;
+      const int64_t s_next = s + tstride * kRows;
+      const bool valid_next = tile + tstride < n_tiles && s_next < pass_end;
+      int r_next = 0;
       // ---- gather: 16 levels x 8 corners -> 32 fp16 features -> operand tile (4 chunks) ----
       uint4 shq0 = make_uint4(0u, 0u, 0u, 0u), shq1 = shq0;
       if (valid) {
-        const int r = __ldg(A.ray_id + s);
-        const float t = __ldg(A.ts + s);
-        const float ox = __ldg(A.rays_o + 3 * r), oy = __ldg(A.rays_o + 3 * r + 1), oz = __ldg(A.rays_o + 3 * r + 2);
-        const float dx = __ldg(A.rays_d + 3 * r), dy = __ldg(A.rays_d + 3 * r + 1), dz = __ldg(A.rays_d + 3 * r + 2);
+        const float t = nt, ox = nox, oy = noy, oz = noz, dx = ndx, dy = ndy, dz = ndz;
+        if (valid_next) { r_next = __ldg(A.ray_id + s_next); nt = __ldg(A.ts + s_next); }
         const float x = fminf(fmaxf(__fdiv_rn(__fmaf_rn(dx, t, ox) - A.xmin[0], A.xden[0]), 0.f), 1.f);
         const float y = fminf(fmaxf(__fdiv_rn(__fmaf_rn(dy, t, oy) - A.xmin[1], A.xden[1]), 0.f), 1.f);
         const float z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(dz, t, oz) - A.xmin[2], A.xden[2]), 0.f), 1.f);
@@ -215,6 +242,11 @@ __global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __re
       tc::fence_before_sync();
       wg_sync(wg);
       if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::g1, s_enc + s * 32);
+      if (valid_next) {      // second hop of the next tile's lookups; lands while this tile runs its five layers
+        if (!valid) { r_next = __ldg(A.ray_id + s_next); nt = __ldg(A.ts + s_next); }
+        nox = __ldg(A.rays_o + 3 * r_next); noy = __ldg(A.rays_o + 3 * r_next + 1); noz = __ldg(A.rays_o + 3 * r_next + 2);
+        ndx = __ldg(A.rays_d + 3 * r_next); ndy = __ldg(A.rays_d + 3 * r_next + 1); ndz = __ldg(A.rays_d + 3 * r_next + 2);
+      }
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       tc_relu_row64(tmem_row, b16, row);
@@ -750,8 +782,20 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
               if (A.g.res[l] <= (uint32_t)agg_long_res) scatter_level_aggregated<5>(gl, L, d0, d1, valid);
               else scatter_level_aggregated<3>(gl, L, d0, d1, valid);
             } else if (valid) {
+              // x-neighbour corners that share an aligned pair of entries (see tc_encode_level) take ONE 16-byte reduction
 #pragma unroll
-              for (int k = 0; k < 8; k++) red_add_f32x2(gl + 2 * (size_t)L.idx[k], L.w[k] * d0, L.w[k] * d1);
+              for (int p = 0; p < 4; p++) {
+                const uint32_t ia = L.idx[2 * p], ib = L.idx[2 * p + 1];
+                const float wa = L.w[2 * p], wb = L.w[2 * p + 1];
+                if ((ia ^ ib) == 1u) {
+                  const bool odd = ia & 1u;
+                  const float lo_w = odd ? wb : wa, hi_w = odd ? wa : wb;
+                  red_add_f32x4(gl + 2 * (size_t)(ia & ~1u), lo_w * d0, lo_w * d1, hi_w * d0, hi_w * d1);
+                } else {
+                  red_add_f32x2(gl + 2 * (size_t)ia, wa * d0, wa * d1);
+                  red_add_f32x2(gl + 2 * (size_t)ib, wb * d0, wb * d1);
+                }
+              }
             }
           }
         }

@@ -49,6 +49,10 @@ __device__ __forceinline__ void red_add_f32x2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
+__device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // Warp-aggregated scatter.  Consecutive lanes are consecutive samples of one ray, so lanes
 // that hit the same coarse entry form RUNS: a segmented warp reduction over runs of equal index
 // (5 shuffle steps) leaves the run total in the run's first lane, which issues one reduction.
