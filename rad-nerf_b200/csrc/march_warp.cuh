@@ -84,6 +84,17 @@ __device__ __forceinline__ int march_ray_warp(const Ray& ray, const MarchParams&
              fabsf(__fsub_rn(p.dt_min, q)) != half_ulp;
       if (fast) mine = __fmaf_rn((float)lane, q, tc);
     }
+    if (!kConstDt && (__float_as_uint(p.esf) & 0x007fffffu) == 0u && __fmul_rn(tc, p.esf) >= p.dt_min && tc >= 1e-30f) {
+      // Exponential stepping with a power-of-two factor (1/256, train_ml.py:101): t*esf is exact, so while the clamp of
+      // calc_dt is inactive over the whole chunk, t + fl(t*esf) = fma(t, esf, t) -- one instruction per chain element
+      // instead of four.  The chain is increasing: the clamp is inactive iff it is at both ends.
+      float m = tc;
+#pragma unroll
+      for (int k = 1; k < 32; k++)
+        if (k <= lane) m = __fmaf_rn(m, p.esf, m);
+      const float c30 = __shfl_sync(kFullMask, m, 30);
+      if (__fmul_rn(c30, p.esf) <= p.dt_max) { mine = m; fast = true; }
+    }
     if (!fast) {
 #pragma unroll
       for (int k = 1; k < 32; k++) {
