@@ -429,6 +429,17 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
                             float* zero_grads, float lr, float beta1, float beta2, float eps, int64_t step,
                             float grad_scale, rnb_stream_t stream);
 
+/* ------------------------------------------------------------------------------------
+ * (callers of the path) Training-batch assembly on the device: replaces BaseDataset.__getitem__'s pixel sampling
+ *     (datasets/base.py:22-29), the index gathers of train_ml.py:183-185 and get_rays (datasets/ray_utils.py:46-70).
+ *     directions (n_pix,3) f32 camera-space directions; poses (n_img,3,4) f32 [R|t]; images (n_img,n_pix,3) f32 or NULL
+ *     (then rgb must be NULL); img_idxs / pix_idxs (B) i64 or NULL = draw iid uniform indices from `seed`.
+ *     out: rays_o, rays_d (B,3) (unnormalised, as the reference), rgb (B,3), and the indices used (may be NULL).
+ * ------------------------------------------------------------------------------------ */
+int rnb_batch_rays(const float* directions, const float* poses, const float* images, const int64_t* img_idxs,
+                   const int64_t* pix_idxs, int64_t n_img, int64_t n_pix, int64_t B, uint64_t seed, float* rays_o,
+                   float* rays_d, float* rgb, int64_t* img_idxs_out, int64_t* pix_idxs_out, rnb_stream_t stream);
+
 /* Optional per-stage device timing of the fused step (CUDA events around every stage; off by default).
  * Stage order: gate, march, scan, expand, field_fwd, composite_fw, blend_loss, composite_bw, field_bwd,
  * gate_bwd, adam.  rnb_engine_profile_read synchronises, returns the accumulated milliseconds and call

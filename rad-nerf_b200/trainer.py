@@ -23,10 +23,17 @@ from .models.networks import MNGP, NGP, Ray_Gate
 from .models.rendering import render
 
 
+def cosine_lr(base_lr, step, total_steps, eta_min_ratio=1.0 / 30):
+    """torch.optim.lr_scheduler.CosineAnnealingLR closed form with eta_min = base_lr / 30 (train_ml.py:150-153)."""
+    import math
+    eta_min = base_lr * eta_min_ratio
+    return eta_min + (base_lr - eta_min) * (1 + math.cos(math.pi * min(step, total_steps) / total_steps)) / 2
+
+
 class Trainer:
     def __init__(self, scale=0.5, K=2, lr=1e-2, log2_T=19, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
                  loss_scale=1024.0, device="cuda", update_interval=16, warmup_steps=256, freeze_occupancy=False,
-                 random_bg=False, seed=0, engine=True, batch_rays=8192, samples_per_ray=128):
+                 random_bg=False, seed=0, engine=True, batch_rays=8192, samples_per_ray=128, total_steps=None):
         self.device = torch.device(device)
         self.K, self.scale = K, scale
         self.exp_step_factor = syn.exp_step_factor_for_scale(scale)
@@ -50,7 +57,9 @@ class Trainer:
         self.global_step = 0
         self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
         self._shadow = None
-        self.lr = lr
+        self.lr = self.base_lr = lr
+        # CosineAnnealingLR(opt, num_epochs * 1000, lr / 30) stepped once per iteration (train_ml.py:143-153); None = constant
+        self.total_steps = total_steps
         self.engine = None
         if engine:
             # the fused step (csrc/engine.cu): same modules, their parameters re-homed into one flat vector
@@ -106,6 +115,10 @@ class Trainer:
         occupancy update, so that every batch is marched against the same bitfields as in the sequential order."""
         if self.global_step % self.update_interval == 0:
             self._grid_update()
+        if self.total_steps:
+            self.lr = cosine_lr(self.base_lr, self.global_step, self.total_steps)
+            for g in self.opt.param_groups:
+                g["lr"] = self.lr
         if self.engine is not None:
             if next_rays is not None and (self.global_step + 1) % self.update_interval == 0:
                 next_rays = None
