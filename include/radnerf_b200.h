@@ -315,6 +315,8 @@ typedef struct {
   int64_t march_slot1;           /* second copy of the marcher's outputs [t_scratch .. deltas] (same internal offsets,
                                   * march_slot_bytes long) for marching the NEXT batch while this one trains      */
   int64_t march_slot_bytes;
+  int64_t coarse;                /* u64 (K,4096): dilated 64^3-block occupancy (bit x of word y + 64 z), part of the march slot; used
+                                  * for the marcher's empty-space test when cascades == 1 and grid_size == 128     */
 } rnb_engine_layout;
 
 int rnb_engine_layout_of(const rnb_engine_config* cfg, rnb_engine_layout* out);
@@ -366,6 +368,7 @@ typedef struct {
   int64_t gate_in, gate_logits, gate_prob, importance;
   int64_t t_cur, t2, acc_opacity, acc_depth, acc_rgb, item_start, item_n, alive0, alive1, counters, seg;
   int64_t ray_id, ts, sigmas, rgb4;
+  int64_t coarse;                /* u64 (K,4096): see rnb_engine_layout.coarse */
 } rnb_render_layout;
 int rnb_render_layout_of(const rnb_engine_config* cfg, rnb_render_layout* out);
 /* out: rgb (R,3), depth (R,K) ungated (Q19), opacity (R); pass_rgb (K,R,3) per-sub-NeRF colours after the

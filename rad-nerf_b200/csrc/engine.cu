@@ -13,6 +13,7 @@
 #include "aabb.cuh"
 #include "composite.cuh"
 #include "march_warp.cuh"
+#include "coarse.cuh"
 
 namespace rnb {
 
@@ -82,7 +83,8 @@ template <bool kConstDt>
 __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                         const float* __restrict__ noise, MarchParams p, BitfieldPtrs bf,
                                                         float cx, float cy, float cz, float hx, float hy, float hz, float near_d,
-                                                        int n_rays, int32_t* __restrict__ counts, float* __restrict__ t_scratch) {
+                                                        int n_rays, int32_t* __restrict__ counts, float* __restrict__ t_scratch,
+                                                        const uint64_t* __restrict__ coarse, float inv_bound) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int pass = blockIdx.y;
   if (r >= n_rays) return;
@@ -92,10 +94,13 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
   float t1 = -1.f, t2 = -1.f;
   if (hit.y > 0) { t1 = fmaxf(hit.x, 0.0f); t2 = hit.y; }
   if (t1 >= 0 && t1 < near_d) t1 = near_d;
+  // empty-space test against the dilated coarse grid (coarse.cuh): skip rays that cannot meet an occupied cell, stop the
+  // others behind the last block they can meet
+  if (coarse != nullptr && t1 >= 0 && t1 < t2) t2 = coarse_last_hit(ray, t1, t2, coarse + (int64_t)pass * kCoarseWords, inv_bound);
   if (t1 >= 0) t1 = __fmaf_rn(calc_dt(t1, p), __ldg(noise + (int64_t)pass * n_rays + r), t1);
   float t_next;
   const int64_t row = (int64_t)pass * n_rays + r;
-  const int n = march_ray_warp<kConstDt>(ray, p, bf.p[pass], t1, t2, p.max_samples, t_scratch + row * p.max_samples, t_next);
+  const int n = t2 < 0 ? 0 : march_ray_warp<kConstDt>(ray, p, bf.p[pass], t1, t2, p.max_samples, t_scratch + row * p.max_samples, t_next);
   if ((threadIdx.x & 31) == 0) counts[row] = n;
 }
 
@@ -394,6 +399,12 @@ struct StageTimer {
 };
 }  // namespace
 
+// the empty-space test of coarse.cuh holds for one cascade of 128^3 cells over [-scale, scale]^3 (RNB_NO_CULL=1 turns it off)
+static bool coarse_enabled(const rnb_engine_config* c) {
+  static const bool off = getenv("RNB_NO_CULL") != nullptr && atoi(getenv("RNB_NO_CULL")) != 0;
+  return !off && c->cascades == 1 && c->grid_size == 2 * kCoarse;
+}
+
 static int check_cfg(const rnb_engine_config* c, const char* what) {
   RNB_REQUIRE(c != nullptr, what);
   RNB_REQUIRE(c->K >= 1 && c->K <= RNB_MAX_K && c->n_rays >= 1 && c->max_samples >= 1 && c->max_samples <= 65536, what);
@@ -418,6 +429,7 @@ int rnb_engine_layout_of(const rnb_engine_config* c, rnb_engine_layout* L) {
   L->counts = w.take(K * R * 4); L->starts = w.take(K * R * 4);
   L->seg = w.take((2 * RNB_MAX_K + 4) * 4);
   L->ray_id = w.take(S * 4); L->ts = w.take(S * 4); L->deltas = w.take(S * 4);
+  L->coarse = w.take(K * kCoarseWords * 8);      // dilated 64^3-block occupancy of every sub-NeRF (coarse.cuh)
   L->enc = w.take(S * 32 * 2); L->rgb_in = w.take(S * 32 * 2); L->geo_h = w.take(S * 64 * 2);
   L->rgb_h1 = w.take(S * 64 * 2); L->rgb_h2 = w.take(S * 64 * 2); L->sraw = w.take(S * 2);
   L->sigmas = w.take(S * 4); L->rgb4 = w.take(S * 4 * 2); L->ws = w.take(S * 4);
@@ -482,12 +494,21 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
   const dim3 ray_grid(ceil_div((int64_t)R * 32, 256), K);
   {
   StageTimer tm(ST_MARCH, st);
+  // single-cascade scenes: conservative coarse occupancy, rebuilt from the bitfields on every call (one ~3 us kernel)
+  uint64_t* coarse = nullptr;
+  if (coarse_enabled(c)) {
+    coarse = (uint64_t*)(ws + L.coarse);
+    if (int rc = coarse_build(bitfields, K, coarse, st)) return rc;
+  }
+  const float inv_bound = 1.0f / c->scale;
   if (c->exp_step_factor == 0.0f)
     eng_march_kernel<true><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2],
-                                                     c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch);
+                                                     c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch,
+                                                     coarse, inv_bound);
   else
     eng_march_kernel<false><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2],
-                                                      c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch);
+                                                      c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch,
+                                                      coarse, inv_bound);
   }
   { StageTimer tm(ST_SCAN, st); eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg); }
   { StageTimer tm(ST_EXPAND, st); eng_expand_kernel<<<ray_grid, 256, 0, st>>>(counts, starts, t_scratch, mp, R, S, ray_id, ts, deltas); }

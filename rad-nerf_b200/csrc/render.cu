@@ -14,9 +14,12 @@
 //                  reference's recurrence (volumerendering.cu:223-249), appends survivors to the next list.
 // NS follows the reference's schedule clamp(N_rays / N_alive, min, 64) (ml_rendering.py:115) with a floor of
 // 8 (Q13: the schedule only matters for the 1024-scheduled-samples cut-off).
+#include <stdlib.h>
+
 #include "aabb.cuh"
 #include "composite.cuh"
 #include "march_warp.cuh"
+#include "coarse.cuh"
 
 namespace rnb {
 
@@ -68,7 +71,8 @@ __device__ __forceinline__ bool locate_item(const PassCounts& C, int K, int64_t 
 template <bool kConstDt>
 __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, MarchParams mp,
                                                         BitfieldPtrsR bf, PassCounts C, int K, int R, int in, int NS, int64_t capacity,
-                                                        InfState S, int32_t* __restrict__ ray_id, float* __restrict__ ts) {
+                                                        InfState S, int32_t* __restrict__ ray_id, float* __restrict__ ts,
+                                                        const uint64_t* __restrict__ coarse, float inv_bound) {
   __shared__ float tbuf[8][64];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   int64_t total = 0;
@@ -79,7 +83,14 @@ __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict_
     const int r = S.alive[in][(int64_t)pass * R + j];
     const int64_t item = (int64_t)pass * R + r;
     const Ray ray = load_ray(rays_o, rays_d, r);
-    const float t = S.t_cur[item], t2 = S.t2[item];
+    const float t = S.t_cur[item];
+    float t2 = S.t2[item];
+    if (coarse != nullptr && t < t2) {
+      // first round only (coarse.cuh): rays that cannot meet an occupied cell end here, the others stop marching behind
+      // the last block they can meet -- in this and in every later round
+      t2 = coarse_last_hit(ray, t, t2, coarse + (int64_t)pass * kCoarseWords, inv_bound);
+      if (lane == 0) S.t2[item] = t2;
+    }
     float t_next = t;
     int n = 0;
     if (t < t2) n = march_ray_warp<kConstDt>(ray, mp, bf.p[pass], t, t2, NS, tbuf[wib], t_next);   // raymarching.cu:365
@@ -197,6 +208,7 @@ int rnb_render_layout_of(const rnb_engine_config* c, rnb_render_layout* L) {
   L->alive0 = take(K * R * 4); L->alive1 = take(K * R * 4); L->counters = take(4 * RNB_MAX_K * 4);
   L->seg = take((2 * RNB_MAX_K + 4) * 4);
   L->ray_id = take(S * 4); L->ts = take(S * 4); L->sigmas = take(S * 4); L->rgb4 = take(S * 8);
+  L->coarse = take(K * kCoarseWords * 8);
   L->total_bytes = off;
   return RNB_OK;
 }
@@ -231,6 +243,11 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
   const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, (float)c->cascades);
   BitfieldPtrsR bf;
   for (int i = 0; i < K; i++) { RNB_REQUIRE(bitfields[i] != nullptr, what); bf.p[i] = bitfields[i]; }
+  uint64_t* coarse = nullptr;
+  if (c->cascades == 1 && c->grid_size == 2 * kCoarse && !(getenv("RNB_NO_CULL") && atoi(getenv("RNB_NO_CULL")))) {
+    coarse = (uint64_t*)(ws + L.coarse);
+    if (int rc = coarse_build(bitfields, K, coarse, st)) return rc;
+  }
   inf_init_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, K, c->center[0], c->center[1], c->center[2], c->half_size[0],
                                                     c->half_size[1], c->half_size[2], c->near_distance, St);
   rnb_field_params P;
@@ -241,17 +258,26 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
   PassCounts C;
   for (int p = 0; p < K; p++) C.n[p] = R;
   const int min_samples = c->exp_step_factor == 0.0f ? 1 : 4;   // ml_rendering.py:108
+  int64_t ns_floor = (S - 128 * (int64_t)K) / ((int64_t)K * R);
+  ns_floor = ns_floor < 8 ? 8 : ns_floor > 64 ? 64 : ns_floor;
+  // RNB_RENDER_PROF=1: per-stage device time of this call on stderr (CUDA events; diagnostics only)
+  const bool prof = getenv("RNB_RENDER_PROF") != nullptr;
+  float t_march = 0.f, t_field = 0.f, t_comp = 0.f;
+  cudaEvent_t ev[4];
+  if (prof) for (int i = 0; i < 4; i++) cudaEventCreate(&ev[i]);
   int scheduled = 0, in = 0, rounds = 0;
   int64_t total_samples = 0;
   while (scheduled < c->max_samples) {
     int64_t alive = 0;
     for (int p = 0; p < K; p++) alive += C.n[p];
     if (alive == 0) break;
-    // N_samples = max(min(N_rays // N_alive, 64), min_samples) (ml_rendering.py:115), floor 8, bounded by the workspace
+    // N_samples = max(min(N_rays // N_alive, 64), min_samples) (ml_rendering.py:115) with a floor set by the workspace the
+    // caller provided (samples per alive item and round that always fit: 8..64).  A warp computes 32 chain elements at a
+    // time, so small budgets re-do marching work round after round; large ones evaluate samples behind a termination.
     int64_t NS = ((int64_t)K * R) / alive;
     if (NS > 64) NS = 64;
     if (NS < min_samples) NS = min_samples;
-    if (NS < 8) NS = 8;
+    if (NS < ns_floor) NS = ns_floor;
     while (NS > 1) {
       int64_t need = 0;
       for (int p = 0; p < K; p++) need += ((int64_t)C.n[p] * NS + 127) / 128 * 128;
@@ -262,22 +288,33 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
     int64_t base = 0;
     for (int p = 0; p < K; p++) { C.base[p] = (int32_t)base; base += ((int64_t)C.n[p] * NS + 127) / 128 * 128; }
     C.base[K] = (int32_t)base;
+    if (prof) cudaEventRecord(ev[0], st);
     inf_round_begin_kernel<<<1, 32, 0, st>>>(St, K, in ^ 1);
     int grid = ceil_div(alive, 8);
     if (grid > kNumSMs * 8) grid = kNumSMs * 8;
     if (c->exp_step_factor == 0.0f)
-      inf_march_kernel<true><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts);
+      inf_march_kernel<true><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts,
+                                                   rounds == 0 ? coarse : nullptr, 1.0f / c->scale);
     else
-      inf_march_kernel<false><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts);
+      inf_march_kernel<false><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts,
+                                                    rounds == 0 ? coarse : nullptr, 1.0f / c->scale);
     inf_seg_kernel<<<1, 32, 0, st>>>(C, K, St.sample_cnt, seg);
     if (int rc = check_launch(what)) return rc;
     rnb_samples Sm = {rays_o, rays_d, ray_id, ts, seg, base > 0 ? base : 128};
+    if (prof) cudaEventRecord(ev[1], st);
     if (int rc = rnb_field_fwd(&P, &Sm, nullptr, sigmas, rgb4, stream)) return rc;
+    if (prof) cudaEventRecord(ev[2], st);
     inf_composite_kernel<<<grid, 256, 0, st>>>(sigmas, rgb4, ts, mp, C, K, R, in, c->T_threshold, S, St);
     if (int rc = check_launch(what)) return rc;
     int32_t host_cnt[2 * RNB_MAX_K + RNB_MAX_K];
     RNB_CUDA(cudaMemcpyAsync(host_cnt, counters, sizeof(int32_t) * 3 * RNB_MAX_K, cudaMemcpyDeviceToHost, st), what);
+    if (prof) cudaEventRecord(ev[3], st);
     RNB_CUDA(cudaStreamSynchronize(st), what);
+    if (prof) {
+      float a = 0.f, b = 0.f, c2 = 0.f;
+      cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]); cudaEventElapsedTime(&c2, ev[2], ev[3]);
+      t_march += a; t_field += b; t_comp += c2;
+    }
     in ^= 1;
     for (int p = 0; p < K; p++) { C.n[p] = host_cnt[in * RNB_MAX_K + p]; total_samples += host_cnt[2 * RNB_MAX_K + p]; }
     rounds++;
@@ -285,6 +322,11 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
   BgR bg;
   for (int i = 0; i < K; i++) for (int k = 0; k < 3; k++) bg.c[i][k] = bg_host[3 * i + k];
   inf_finish_kernel<<<ceil_div(R, 256), 256, 0, st>>>(St, (const float*)(ws + L.gate_prob), bg, R, K, rgb, depth, opacity, pass_rgb);
+  if (prof) {
+    fprintf(stderr, "[rnb_render] rays %d K %d rounds %d samples %lld: march %.3f ms, field %.3f ms, composite+readback %.3f ms\n", R, K, rounds,
+            (long long)total_samples, t_march, t_field, t_comp);
+    for (int i = 0; i < 4; i++) cudaEventDestroy(ev[i]);
+  }
   if (stats_host) { stats_host[0] = total_samples; stats_host[1] = rounds; }
   return check_launch(what);
 }

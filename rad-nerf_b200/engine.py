@@ -38,7 +38,7 @@ class _Config(ctypes.Structure):
 _LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_hidden", "gate_logits", "gate_dlogits", "gate_prob", "dgate", "importance",
                   "t_scratch", "counts", "starts", "seg", "ray_id", "ts", "deltas", "enc", "rgb_in", "geo_h", "rgb_h1", "rgb_h2",
                   "sraw", "sigmas", "rgb4", "ws", "dsigmas", "drgbs", "pass_opacity", "pass_depth", "pass_rgb", "pass_total",
-                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss", "march_slot1", "march_slot_bytes"]
+                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss", "march_slot1", "march_slot_bytes", "coarse"]
 
 
 class _Layout(ctypes.Structure):
@@ -46,7 +46,7 @@ class _Layout(ctypes.Structure):
 
 
 _RENDER_LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_logits", "gate_prob", "importance", "t_cur", "t2", "acc_opacity", "acc_depth",
-                         "acc_rgb", "item_start", "item_n", "alive0", "alive1", "counters", "seg", "ray_id", "ts", "sigmas", "rgb4"]
+                         "acc_rgb", "item_start", "item_n", "alive0", "alive1", "counters", "seg", "ray_id", "ts", "sigmas", "rgb4", "coarse"]
 
 
 class _RenderLayout(ctypes.Structure):

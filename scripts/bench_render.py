@@ -37,9 +37,10 @@ def main():
         o, d = syn.full_image_rays(cam, 3)
         o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
         eng = tr.engine
-        eng.render(o, d)
-        ms, res = timed(lambda: eng.render(o, d), 3)
-        line = {"workload": name, "rays": int(o.shape[0]), "K": w["K"], "fused_ms": round(ms, 3),
+        spr = int(os.environ.get("RNB_RENDER_SPR", "16"))
+        eng.render(o, d, samples_per_ray=spr)
+        ms, res = timed(lambda: eng.render(o, d, samples_per_ray=spr), 3)
+        line = {"workload": name, "rays": int(o.shape[0]), "K": w["K"], "samples_per_round": spr, "fused_ms": round(ms, 3),
                 "samples": int(res["total_samples"]), "rounds": int(res["rounds"]),
                 "Msamples_per_s": round(res["total_samples"] / ms / 1e3, 1)}
         if os.environ.get("RNB_SKIP_PY") != "1":
