@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256) eng_gate_softmax_kernel(const __half* __r
 // ---- marching of all K passes -------------------------------------------------------------------------
 struct BitfieldPtrs { const uint8_t* p[RNB_MAX_K]; };
 
-template <bool kConstDt>
+template <bool kConstDt, bool kOneCascade>
 __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d,
                                                         const float* __restrict__ noise, MarchParams p, BitfieldPtrs bf,
                                                         float cx, float cy, float cz, float hx, float hy, float hz, float near_d,
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
   if (t1 >= 0) t1 = __fmaf_rn(calc_dt(t1, p), __ldg(noise + (int64_t)pass * n_rays + r), t1);
   float t_next;
   const int64_t row = (int64_t)pass * n_rays + r;
-  const int n = t2 < 0 ? 0 : march_ray_warp<kConstDt>(ray, p, bf.p[pass], t1, t2, p.max_samples, t_scratch + row * p.max_samples, t_next);
+  const int n = t2 < 0 ? 0 : march_ray_warp<kConstDt, kOneCascade>(ray, p, bf.p[pass], t1, t2, p.max_samples, t_scratch + row * p.max_samples, t_next);
   if ((threadIdx.x & 31) == 0) counts[row] = n;
 }
 
@@ -501,14 +501,14 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
     if (int rc = coarse_build(bitfields, K, coarse, st)) return rc;
   }
   const float inv_bound = 1.0f / c->scale;
-  if (c->exp_step_factor == 0.0f)
-    eng_march_kernel<true><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2],
-                                                     c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch,
-                                                     coarse, inv_bound);
-  else
-    eng_march_kernel<false><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2],
-                                                      c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R, counts, t_scratch,
-                                                      coarse, inv_bound);
+#define RNB_ENG_MARCH(CONST_DT, ONE)                                                                                              \
+  eng_march_kernel<CONST_DT, ONE><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2], \
+                                                            c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R,  \
+                                                            counts, t_scratch, coarse, inv_bound)
+  if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_ENG_MARCH(true, true);     // bounded scenes (train_ml.py:99-101)
+  else if (c->exp_step_factor == 0.0f) RNB_ENG_MARCH(true, false);
+  else RNB_ENG_MARCH(false, false);
+#undef RNB_ENG_MARCH
   }
   { StageTimer tm(ST_SCAN, st); eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg); }
   { StageTimer tm(ST_EXPAND, st); eng_expand_kernel<<<ray_grid, 256, 0, st>>>(counts, starts, t_scratch, mp, R, S, ray_id, ts, deltas); }

@@ -68,7 +68,7 @@ __device__ __forceinline__ bool locate_item(const PassCounts& C, int K, int64_t 
   return false;
 }
 
-template <bool kConstDt>
+template <bool kConstDt, bool kOneCascade>
 __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, MarchParams mp,
                                                         BitfieldPtrsR bf, PassCounts C, int K, int R, int in, int NS, int64_t capacity,
                                                         InfState S, int32_t* __restrict__ ray_id, float* __restrict__ ts,
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict_
     }
     float t_next = t;
     int n = 0;
-    if (t < t2) n = march_ray_warp<kConstDt>(ray, mp, bf.p[pass], t, t2, NS, tbuf[wib], t_next);   // raymarching.cu:365
+    if (t < t2) n = march_ray_warp<kConstDt, kOneCascade>(ray, mp, bf.p[pass], t, t2, NS, tbuf[wib], t_next);   // raymarching.cu:365
     __syncwarp();
     int start = 0;
     if (lane == 0 && n > 0) start = atomicAdd(S.sample_cnt + pass, n);
@@ -292,12 +292,13 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
     inf_round_begin_kernel<<<1, 32, 0, st>>>(St, K, in ^ 1);
     int grid = ceil_div(alive, 8);
     if (grid > kNumSMs * 8) grid = kNumSMs * 8;
-    if (c->exp_step_factor == 0.0f)
-      inf_march_kernel<true><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts,
-                                                   rounds == 0 ? coarse : nullptr, 1.0f / c->scale);
-    else
-      inf_march_kernel<false><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts,
-                                                    rounds == 0 ? coarse : nullptr, 1.0f / c->scale);
+#define RNB_INF_MARCH(CONST_DT, ONE)                                                                                  \
+  inf_march_kernel<CONST_DT, ONE><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts, \
+                                                        rounds == 0 ? coarse : nullptr, 1.0f / c->scale)
+    if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_INF_MARCH(true, true);
+    else if (c->exp_step_factor == 0.0f) RNB_INF_MARCH(true, false);
+    else RNB_INF_MARCH(false, false);
+#undef RNB_INF_MARCH
     inf_seg_kernel<<<1, 32, 0, st>>>(C, K, St.sample_cnt, seg);
     if (int rc = check_launch(what)) return rc;
     rnb_samples Sm = {rays_o, rays_d, ray_id, ts, seg, base > 0 ? base : 128};
