@@ -203,3 +203,35 @@ WORKLOADS = {
     "radnerf_360_k4": dict(scale=16.0, K=4, H=822, W=1237, fx=1050.0, radius=1.0),
     "radnerf_tat_k8_infer": dict(scale=0.5, K=8, H=1080, W=1920, fx=1166.0, radius=0.9),
 }
+
+
+def analytic_colors(scene: Scene, rays_o, rays_d, background: float = 1.0):
+    """Ground-truth colours of `scene` for CUDA rays (B,3): the analytic density / colour integrated along the
+    reference's own constant-step marching (dt = sqrt(3)/1024 through the scene's occupancy bitfield) and composited
+    by the vren operators, blended on a uniform background.  Used to fit a model against the synthetic scene
+    (scripts/fit_scene.py, tests/test_fit_gpu.py); bounded scenes only."""
+    import torch
+    from . import vren
+    assert scene.cascades == 1, "bounded scenes only"
+    dev = rays_o.device
+    bf = torch.from_numpy(packbits_np(scene.density_grid, scene.threshold)).to(dev)
+    center = torch.zeros(1, 3, device=dev); half = torch.full((1, 3), float(scene.scale), device=dev)
+    out = torch.empty(rays_o.shape[0], 3, device=dev)
+    mus = torch.from_numpy(scene.mus).to(dev); sg = torch.from_numpy(scene.sig).to(dev); amp = torch.from_numpy(scene.amp).to(dev)
+    for s in range(0, rays_o.shape[0], 1 << 16):
+        o, d = rays_o[s:s + (1 << 16)].contiguous(), rays_d[s:s + (1 << 16)].contiguous()
+        _, hits_t, _ = vren.ray_aabb_intersect(o, d, center, half, 1)
+        h = hits_t[:, 0].contiguous()
+        h[(h[:, 0] >= 0) & (h[:, 0] < NEAR_DISTANCE), 0] = NEAR_DISTANCE
+        noise = torch.full((o.shape[0],), 0.5, device=dev)
+        rays_a, xyzs, _, deltas, ts, counter = vren.raymarching_train(o, d, h, bf, 1, float(scene.scale), 0.0, noise, GRID_SIZE, 1024)
+        n = int(counter[0])
+        x = xyzs[:n]
+        sigma = torch.zeros(n, device=dev)
+        for j in range(mus.shape[0]):
+            d2 = ((x - mus[j]) ** 2).sum(1)
+            sigma += amp[j] * torch.exp(-d2 / (2 * sg[j] * sg[j])) * (d2 < (4 * sg[j]) ** 2)
+        rgb = (0.5 + 0.5 * torch.sin(8.0 * x)).contiguous()
+        _, opacity, _, col, _ = vren.composite_train_fw(sigma, rgb, deltas[:n].contiguous(), ts[:n].contiguous(), rays_a, 1e-4)
+        out[s:s + o.shape[0]] = col + background * (1 - opacity[:, None])
+    return out
