@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
                                                         const float* __restrict__ noise, MarchParams p, BitfieldPtrs bf,
                                                         float cx, float cy, float cz, float hx, float hy, float hz, float near_d,
                                                         int n_rays, int32_t* __restrict__ counts, float* __restrict__ t_scratch,
-                                                        const uint64_t* __restrict__ coarse, float inv_bound) {
+                                                        const uint64_t* __restrict__ coarse) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int pass = blockIdx.y;
   if (r >= n_rays) return;
@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
   if (t1 >= 0 && t1 < near_d) t1 = near_d;
   // empty-space test against the dilated coarse grid (coarse.cuh): skip rays that cannot meet an occupied cell, stop the
   // others behind the last block they can meet
-  if (coarse != nullptr && t1 >= 0 && t1 < t2) t2 = coarse_last_hit(ray, t1, t2, coarse + (int64_t)pass * kCoarseWords, inv_bound);
+  if (coarse != nullptr && t1 >= 0 && t1 < t2) t2 = coarse_last_hit(ray, t1, t2, coarse + (int64_t)pass * p.cascades * kCoarseWords, p.cascades, p.scale);
   if (t1 >= 0) t1 = __fmaf_rn(calc_dt(t1, p), __ldg(noise + (int64_t)pass * n_rays + r), t1);
   float t_next;
   const int64_t row = (int64_t)pass * n_rays + r;
@@ -399,10 +399,10 @@ struct StageTimer {
 };
 }  // namespace
 
-// the empty-space test of coarse.cuh holds for one cascade of 128^3 cells over [-scale, scale]^3 (RNB_NO_CULL=1 turns it off)
+// the empty-space test of coarse.cuh is written for cascades of 128^3 cells (RNB_NO_CULL=1 turns it off)
 static bool coarse_enabled(const rnb_engine_config* c) {
   static const bool off = getenv("RNB_NO_CULL") != nullptr && atoi(getenv("RNB_NO_CULL")) != 0;
-  return !off && c->cascades == 1 && c->grid_size == 2 * kCoarse;
+  return !off && c->grid_size == 2 * kCoarse;
 }
 
 static int check_cfg(const rnb_engine_config* c, const char* what) {
@@ -429,7 +429,7 @@ int rnb_engine_layout_of(const rnb_engine_config* c, rnb_engine_layout* L) {
   L->counts = w.take(K * R * 4); L->starts = w.take(K * R * 4);
   L->seg = w.take((2 * RNB_MAX_K + 4) * 4);
   L->ray_id = w.take(S * 4); L->ts = w.take(S * 4); L->deltas = w.take(S * 4);
-  L->coarse = w.take(K * kCoarseWords * 8);      // dilated 64^3-block occupancy of every sub-NeRF (coarse.cuh)
+  L->coarse = w.take((int64_t)K * c->cascades * kCoarseWords * 8);      // dilated 64^3-block occupancy of every sub-NeRF (coarse.cuh)
   L->enc = w.take(S * 32 * 2); L->rgb_in = w.take(S * 32 * 2); L->geo_h = w.take(S * 64 * 2);
   L->rgb_h1 = w.take(S * 64 * 2); L->rgb_h2 = w.take(S * 64 * 2); L->sraw = w.take(S * 2);
   L->sigmas = w.take(S * 4); L->rgb4 = w.take(S * 4 * 2); L->ws = w.take(S * 4);
@@ -494,17 +494,16 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
   const dim3 ray_grid(ceil_div((int64_t)R * 32, 256), K);
   {
   StageTimer tm(ST_MARCH, st);
-  // single-cascade scenes: conservative coarse occupancy, rebuilt from the bitfields on every call (one ~3 us kernel)
+  // conservative coarse occupancy of every cascade, rebuilt from the bitfields on every call (one small kernel)
   uint64_t* coarse = nullptr;
   if (coarse_enabled(c)) {
     coarse = (uint64_t*)(ws + L.coarse);
-    if (int rc = coarse_build(bitfields, K, coarse, st)) return rc;
+    if (int rc = coarse_build(bitfields, K, c->cascades, coarse, st)) return rc;
   }
-  const float inv_bound = 1.0f / c->scale;
 #define RNB_ENG_MARCH(CONST_DT, ONE)                                                                                              \
   eng_march_kernel<CONST_DT, ONE><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2], \
                                                             c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R,  \
-                                                            counts, t_scratch, coarse, inv_bound)
+                                                            counts, t_scratch, coarse)
   if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_ENG_MARCH(true, true);     // bounded scenes (train_ml.py:99-101)
   else if (c->exp_step_factor == 0.0f) RNB_ENG_MARCH(true, false);
   else RNB_ENG_MARCH(false, false);

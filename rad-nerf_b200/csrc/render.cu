@@ -72,7 +72,7 @@ template <bool kConstDt, bool kOneCascade>
 __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, MarchParams mp,
                                                         BitfieldPtrsR bf, PassCounts C, int K, int R, int in, int NS, int64_t capacity,
                                                         InfState S, int32_t* __restrict__ ray_id, float* __restrict__ ts,
-                                                        const uint64_t* __restrict__ coarse, float inv_bound) {
+                                                        const uint64_t* __restrict__ coarse) {
   __shared__ float tbuf[8][64];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   int64_t total = 0;
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict_
     if (coarse != nullptr && t < t2) {
       // first round only (coarse.cuh): rays that cannot meet an occupied cell end here, the others stop marching behind
       // the last block they can meet -- in this and in every later round
-      t2 = coarse_last_hit(ray, t, t2, coarse + (int64_t)pass * kCoarseWords, inv_bound);
+      t2 = coarse_last_hit(ray, t, t2, coarse + (int64_t)pass * mp.cascades * kCoarseWords, mp.cascades, mp.scale);
       if (lane == 0) S.t2[item] = t2;
     }
     float t_next = t;
@@ -208,7 +208,7 @@ int rnb_render_layout_of(const rnb_engine_config* c, rnb_render_layout* L) {
   L->alive0 = take(K * R * 4); L->alive1 = take(K * R * 4); L->counters = take(4 * RNB_MAX_K * 4);
   L->seg = take((2 * RNB_MAX_K + 4) * 4);
   L->ray_id = take(S * 4); L->ts = take(S * 4); L->sigmas = take(S * 4); L->rgb4 = take(S * 8);
-  L->coarse = take(K * kCoarseWords * 8);
+  L->coarse = take((int64_t)K * c->cascades * kCoarseWords * 8);
   L->total_bytes = off;
   return RNB_OK;
 }
@@ -244,9 +244,9 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
   BitfieldPtrsR bf;
   for (int i = 0; i < K; i++) { RNB_REQUIRE(bitfields[i] != nullptr, what); bf.p[i] = bitfields[i]; }
   uint64_t* coarse = nullptr;
-  if (c->cascades == 1 && c->grid_size == 2 * kCoarse && !(getenv("RNB_NO_CULL") && atoi(getenv("RNB_NO_CULL")))) {
+  if (c->grid_size == 2 * kCoarse && !(getenv("RNB_NO_CULL") && atoi(getenv("RNB_NO_CULL")))) {
     coarse = (uint64_t*)(ws + L.coarse);
-    if (int rc = coarse_build(bitfields, K, coarse, st)) return rc;
+    if (int rc = coarse_build(bitfields, K, c->cascades, coarse, st)) return rc;
   }
   inf_init_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, K, c->center[0], c->center[1], c->center[2], c->half_size[0],
                                                     c->half_size[1], c->half_size[2], c->near_distance, St);
@@ -294,7 +294,7 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
     if (grid > kNumSMs * 8) grid = kNumSMs * 8;
 #define RNB_INF_MARCH(CONST_DT, ONE)                                                                                  \
   inf_march_kernel<CONST_DT, ONE><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts, \
-                                                        rounds == 0 ? coarse : nullptr, 1.0f / c->scale)
+                                                        rounds == 0 ? coarse : nullptr)
     if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_INF_MARCH(true, true);
     else if (c->exp_step_factor == 0.0f) RNB_INF_MARCH(true, false);
     else RNB_INF_MARCH(false, false);
