@@ -872,13 +872,20 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   A.K = P->K;
   A.rays_o = S->rays_o; A.rays_d = S->rays_d; A.ray_id = S->ray_id; A.ts = S->ts; A.seg = S->seg; A.capacity = S->capacity;
   // levels whose cells are coarser than a few marching steps: runs of consecutive samples of a ray share corner
-  // entries there, so the warp combines them before issuing reductions (measured: profiles/r01_ab_agg_levels.txt)
+  // entries there, so the warp combines them before issuing reductions.  What counts is the cell size in WORLD units
+  // against the step: the resolution thresholds tuned on the unit box (128 / 48: profiles/r01_ab_agg_levels.txt) grow
+  // with the extent of the encoded box -- in a scale-16 scene most samples sit near the centre, where a res-921 cell
+  // still holds ~6 of them, and without combining them the reductions serialise on a few L2 addresses
+  // (field_bwd 1.06 -> 0.70 ms on the 6-cascade workload: profiles/r01_ab_agg_levels.txt)
+  const float extent = P->xyz_max[0] - P->xyz_min[0];
+  const float grow = fmaxf(1.0f, 1.3f * sqrtf(fmaxf(extent, 0.0f)));
   int n_agg = 0;
   for (int l = 0; l < A.g.n_levels; l++)
-    if (A.g.res[l] <= 128) n_agg = l + 1;
+    if ((float)A.g.res[l] <= 128.0f * grow) n_agg = l + 1;
   if (const char* e = getenv("RNB_AGG_LEVELS")) n_agg = atoi(e);   // tuning knob (profiles/): levels with warp-aggregated reductions
+  if (n_agg > A.g.n_levels) n_agg = A.g.n_levels;
   while (n_agg > 0 && A.g.res[n_agg - 1] >= 1024) n_agg--;          // the cell key holds 10-11 bits per axis
-  int agg_long_res = 48;                                            // levels up to this resolution combine whole-warp runs
+  int agg_long_res = (int)(48.0f * grow);                           // levels up to this resolution combine whole-warp runs
   if (const char* e = getenv("RNB_AGG_LONG_RES")) agg_long_res = atoi(e);
   static bool attr_set = false;
   if (!attr_set) {
