@@ -223,3 +223,77 @@ class Ray_Gate(nn.Module):
     def freeze_dict(self):
         for _, param in self.named_parameters():
             param.requires_grad_(False)
+
+
+class unshared_MNGP(nn.Module, _OccupancyMixin):
+    """Ablation of MNGP without parameter sharing: every sub-NeRF owns its hash grid, SH encoder, geo / rgb MLPs and
+    occupancy grid (xyz_encoder_i, dir_encoder_i, geo_net_i, rgb_net_i, density_grid_i, density_bitfield_i); same call
+    interface as MNGP, so ml_render drives it unchanged.  Reference: networks.py:424-628."""
+
+    def __init__(self, scale, rgb_act="Sigmoid", size=2, t=19):
+        super().__init__()
+        self.rgb_act = rgb_act
+        self.scale = scale
+        self.size = size
+        self.register_buffer("center", torch.zeros(1, 3))
+        self.register_buffer("xyz_min", -torch.ones(1, 3) * scale)
+        self.register_buffer("xyz_max", torch.ones(1, 3) * scale)
+        self.register_buffer("half_size", (self.xyz_max - self.xyz_min) / 2)
+        self.cascades = max(1 + int(np.ceil(np.log2(2 * scale))), 1)
+        self.grid_size = GRID_SIZE
+        self.register_buffer("grid_coords", _all_grid_coords(self.grid_size))
+        for i in range(size):
+            self.register_buffer(f"density_bitfield_{i}", torch.zeros(self.cascades * self.grid_size ** 3 // 8, dtype=torch.uint8))
+            self.register_buffer(f"density_grid_{i}", torch.zeros(self.cascades, self.grid_size ** 3))
+            setattr(self, f"xyz_encoder_{i}", _grid_encoder(scale, t))
+            setattr(self, f"dir_encoder_{i}", tcnn.Encoding(3, {"otype": "SphericalHarmonics", "degree": 4}))
+            setattr(self, f"geo_net_{i}", _mlp(32, 16 + 1, 1, "None", seed=100 + i))
+            setattr(self, f"rgb_net_{i}", _mlp(32, 3, 2, rgb_act, seed=200 + i))
+
+    def density(self, x, ind, return_feat=False):
+        x = ((x - self.xyz_min) / (self.xyz_max - self.xyz_min)).clip(0.0, 1.0)
+        h = getattr(self, f"geo_net_{ind}")(getattr(self, f"xyz_encoder_{ind}")(x))
+        sigmas = TruncExp.apply(h[:, 0])
+        return (sigmas, h[..., 1:]) if return_feat else sigmas
+
+    def forward(self, x, d, ind, **kwargs):
+        sigmas, h = self.density(x, ind, return_feat=True)
+        d = getattr(self, f"dir_encoder_{ind}")((d / torch.norm(d, dim=1, keepdim=True) + 1) / 2)
+        return sigmas, getattr(self, f"rgb_net_{ind}")(torch.cat([d, h], 1))
+
+    @torch.no_grad()
+    def sample_uniform_and_occupied_cells(self, M, density_threshold, ind):
+        return self._sample_cells(getattr(self, f"density_grid_{ind}"), M, density_threshold)
+
+    update_density_grid = MNGP.update_density_grid
+    register_bbox = MNGP.register_bbox
+
+
+class NGP_zoo(nn.Module):
+    """`size` independent Instant-NGP fields (model_0 .. model_{size-1}) blended by a gate in moe_render -- the
+    "mixture of whole NGPs" baseline.  Reference: networks.py:1100-1163."""
+
+    def __init__(self, scale, rgb_act="Sigmoid", size=10, t=19):
+        super().__init__()
+        self.rgb_act = rgb_act
+        self.scale = scale
+        self.size = size
+        self.register_buffer("center", torch.zeros(1, 3))
+        self.register_buffer("xyz_min", -torch.ones(1, 3) * scale)
+        self.register_buffer("xyz_max", torch.ones(1, 3) * scale)
+        self.register_buffer("half_size", (self.xyz_max - self.xyz_min) / 2)
+        for i in range(size):
+            setattr(self, f"model_{i}", NGP(scale=scale, rgb_act=rgb_act, t=t))
+
+    def models(self):
+        return [getattr(self, f"model_{i}") for i in range(self.size)]
+
+    @torch.no_grad()
+    def update_density_grid(self, density_threshold, warmup=False, decay=0.95, erode=False):
+        for m in self.models():
+            m.update_density_grid(density_threshold, warmup=warmup, decay=decay, erode=erode)
+
+    @torch.no_grad()
+    def register_bbox(self, bbox):
+        for m in self.models():
+            m.register_bbox(bbox)

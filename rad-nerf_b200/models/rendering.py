@@ -22,3 +22,27 @@ def render(model, rays_o, rays_d, **kwargs):
                 v = v.numpy()
         results[k] = v
     return results
+
+
+def moe_render(model_zoo, gating_net, rays_o, rays_d, warmup=False, **kwargs):
+    """Gated blend of `model_zoo.size` independent NGPs (NGP_zoo): every member renders every ray through its own
+    scene box / occupancy grid, rgb = sum_i g_i rgb_i, opacity = sum_i g_i opacity_i, depth[:, i] = depth_i.
+    Reference: models/rendering.py:48-110.  -> dict rgb, depth (N,size), opacity, gating_code, gating_importance."""
+    rays_o = rays_o.contiguous(); rays_d = rays_d.contiguous()
+    kwargs["return_gate"] = False
+    with torch.autocast("cuda", enabled=rays_o.is_cuda):
+        gate_in = rays_o if gating_net.type == "position" else torch.cat((rays_o, rays_d), 1)
+        gating_code, gating_importance, _ = gating_net(gate_in, warmup)
+        n = rays_o.shape[0]
+        depth = torch.zeros(n, model_zoo.size, device=rays_o.device)
+        rgb = torch.zeros_like(rays_o)
+        opacity = torch.zeros(n, device=rays_o.device)
+        fn = render_rays_test if kwargs.get("test_time", False) else render_rays_train
+        for i in range(model_zoo.size):
+            model = getattr(model_zoo, f"model_{i}")
+            hits_t = intersect_scene_box(model, rays_o, rays_d)
+            res = fn(model, lambda x, d, _m=model, **kw: _m(x, d, **kw), model.density_bitfield, rays_o, rays_d, hits_t, **dict(kwargs))
+            rgb = rgb + res["rgb"] * gating_code[:, i][:, None]
+            depth[:, i] = res["depth"]
+            opacity = opacity + res["opacity"] * gating_code[:, i]
+    return {"rgb": rgb, "depth": depth, "opacity": opacity, "gating_code": gating_code, "gating_importance": gating_importance}
