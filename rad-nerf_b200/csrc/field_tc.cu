@@ -23,7 +23,7 @@
 
 namespace rnb {
 
-constexpr int kWG = 4;            // warpgroups per CTA (forward)
+constexpr int kWG = 5;            // warpgroups per CTA (forward): 640 threads x 96 registers
 constexpr int kRows = 128;        // samples per tile
 
 struct TcFieldArgs {
@@ -92,12 +92,14 @@ struct TcSmem {
   static constexpr int r2 = r1 + 64 * 32 * 2;  // 64 x 64
   static constexpr int r3 = r2 + 64 * 64 * 2;  // 16 x 64
   static constexpr int wend = r3 + 16 * 64 * 2;
-  // per warpgroup: a 128x32 operand tile (encoding, then rgb input) and two 128x64 tiles (hidden activations; the
-  // second one takes rgb hidden 2 so that the bulk store of rgb hidden 1 never races with the next epilogue)
+  // per warpgroup: a 128x32 operand tile (encoding, then rgb input) and a 128x64 tile (the hidden activations in turn).
+  // 24 KB per warpgroup, 142 KB per CTA of 5 warpgroups: the rest of the SM's 256 KB stays L1 (~90 KB) for the table
+  // gathers, which is worth more than a second 128x64 tile.  Measured forward time on the K=2 training shape:
+  // 40 KB/warpgroup: 3 WG 0.158, 4 WG 0.157, 5 WG (227 KB, L1 ~29 KB) 0.215 ms; 24 KB/warpgroup: 4 WG 0.149, 5 WG 0.140,
+  // 6 WG (80 registers) 0.173 ms
   static constexpr int a8 = 0;
   static constexpr int b16 = kRows * 32 * 2;
-  static constexpr int b16b = b16 + kRows * 64 * 2;
-  static constexpr int per_wg = b16b + kRows * 64 * 2;
+  static constexpr int per_wg = b16 + kRows * 64 * 2;
   static constexpr int wg0 = (wend + 127) / 128 * 128;
   static constexpr int bars = wg0 + kWG * per_wg;       // kWG mbarriers
   static constexpr int tmem_slot = bars + kWG * 8;
@@ -139,7 +141,8 @@ __device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* til
 // activations are saved for the backward pass, copy the operand tile the MMAs read -- it already has the layout the
 // backward kernel wants -- to global memory with one bulk store.  A tile is overwritten at the earliest in the
 // epilogue of the FOLLOWING step; this thread confirms that the previous step's store has finished reading its tile
-// before it issues (and commits) this step's MMAs, and everybody waits for those, so no extra signalling is needed.
+// before it issues (and commits) this step's MMAs, and everybody waits for those, so no extra signalling is needed
+// (one exception: rgb hidden 2 overwrites rgb hidden 1 in the epilogue of the SAME step, see there).
 template <bool kSave, int N, int KDIM>
 __device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint32_t a_smem, uint32_t w_smem, __half* save_tile) {
   if (kSave) tc::bulk_wait_read();
@@ -153,7 +156,7 @@ __device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint
 }
 
 template <bool kSave>
-__global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __restrict__ s_enc, __half* __restrict__ s_rgb_in,
+__global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __restrict__ s_enc, __half* __restrict__ s_rgb_in,
                                                                      __half* __restrict__ s_geo_h, __half* __restrict__ s_rgb_h1,
                                                                      __half* __restrict__ s_rgb_h2, __half* __restrict__ s_sraw,
                                                                      float* __restrict__ sigmas, __half* __restrict__ rgb4) {
@@ -161,7 +164,7 @@ __global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __re
   const int tid = threadIdx.x, wg = tid >> 7, row = tid & 127, warp = tid >> 5;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcSmem::tmem_slot);
-  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
   if (tid < kWG) tc::mbar_init(bars + tid, 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   tc::fence_before_sync();
@@ -171,8 +174,7 @@ __global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __re
   const uint32_t tmem_row = tmem_d + ((uint32_t)((warp & 3) * 32) << 16);     // + this warp's 32 lanes
   unsigned char* a8 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::a8;
   unsigned char* b16 = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::b16;
-  unsigned char* b16b = smem + TcSmem::wg0 + wg * TcSmem::per_wg + TcSmem::b16b;
-  const uint32_t a8_s = tc::smem_u32(a8), b16_s = tc::smem_u32(b16), b16b_s = tc::smem_u32(b16b), w_s = tc::smem_u32(smem);
+  const uint32_t a8_s = tc::smem_u32(a8), b16_s = tc::smem_u32(b16), w_s = tc::smem_u32(smem);
   uint64_t* bar = bars + wg;
   uint32_t phase = 0;
   const int K = A.K;
@@ -292,12 +294,18 @@ __global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __re
       if (row == 0) tc_fwd_step<kSave, 64, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r2, s_rgb_h1 + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
-      tc_relu_row64(tmem_row, b16b, row);
+      if (kSave) {
+        // rgb hidden 2 goes into the tile whose previous content (rgb hidden 1) is being copied out by the bulk store
+        // issued a moment ago, next to the MMAs that have now completed: confirm the store has read the tile
+        if (row == 0) tc::bulk_wait_read();
+        wg_sync(wg);
+      }
+      tc_relu_row64(tmem_row, b16, row);
       // ---- rgb layer 3: 64 -> 16, sigmoid ----
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16b_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64);
+      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       {
@@ -315,7 +323,7 @@ __global__ void __maxnreg__(104) field_fwd_tc_kernel(TcFieldArgs A, __half* __re
   if (kSave && row == 0) tc::bulk_wait_all();
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+  if (warp == 0) tc::tmem_dealloc(*tmem_slot, 512);
 }
 
 
@@ -355,7 +363,7 @@ __global__ void __launch_bounds__(kWG * 128, 1) density_cells_tc_kernel(TcFieldA
   const int tid = threadIdx.x, wg = tid >> 7, row = tid & 127, warp = tid >> 5;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + TcSmem::tmem_slot);
-  if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+  if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
   if (tid < kWG) tc::mbar_init(bars + tid, 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   tc::fence_before_sync();
@@ -440,7 +448,7 @@ __global__ void __launch_bounds__(kWG * 128, 1) density_cells_tc_kernel(TcFieldA
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+  if (warp == 0) tc::tmem_dealloc(*tmem_slot, 512);
 }
 
 // ================================ backward on tcgen05 ================================================
