@@ -293,19 +293,31 @@ def run_product(args):
             loss_evt[j].synchronize()
             losses.append(float(loss_pin[j][0]))
 
+    feeder = None
+
     def e2e_step(s):
-        # every step uploads ONE batch from pinned host memory (the next one when marching ahead, so that its rays are
-        # on the device in time) and reads the step's loss back
+        # every step uploads ONE batch from pinned host memory and reads the step's loss back.  The upload goes through
+        # the library's HostFeeder: batch s+1 is copied on a copy stream while step s computes (when marching ahead it is
+        # also the batch whose rays are marched on the side stream), so the copy never sits between two kernels
+        nonlocal feeder
         flush_l2()
-        if not ahead:
-            o, d, t = (a.cuda(non_blocking=True) for a in host[s % len(host)])
-            tr.step(o, d, t)
-        else:
+        if feeder is None:
+            from radnerf_b200.data import HostFeeder
+            feeder = HostFeeder(host, f"cuda:{local}", depth=4)
+        if os.environ.get("RNB_E2E_INLINE_COPY") == "1":     # A/B: copies on the step's own stream
             if s not in staged:
                 staged[s] = tuple(a.cuda(non_blocking=True) for a in host[s % len(host)])
             staged[s + 1] = tuple(a.cuda(non_blocking=True) for a in host[(s + 1) % len(host)])
             o, d, t = staged.pop(s)
-            tr.step(o, d, t, next_rays=staged[s + 1][:2])
+            tr.step(o, d, t, next_rays=staged[s + 1][:2] if ahead else None)
+        else:
+            o, d, t = feeder.get(s)
+            if not ahead:
+                tr.step(o, d, t)
+            else:
+                nxt = feeder.peek(s + 1)
+                tr.step(o, d, t, next_rays=nxt[:2])
+            feeder.done(s)
         read_back(s, tr.engine.loss if tr.engine is not None else tr.last_loss.reshape(1).expand(8))
 
     if ahead and os.environ.get("RNB_BENCH_PRIO", "1") == "1":

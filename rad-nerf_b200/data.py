@@ -46,3 +46,57 @@ class RaySampler:
         call("rnb_batch_rays", self.directions, self.poses, self.images, img_idxs, pix_idxs, i64(self.poses.shape[0]),
              i64(self.directions.shape[0]), i64(B), ctypes.c_uint64((self.seed << 32) + self.calls), o, d, rgb, io, po, stream_arg(dev))
         return (o, d, rgb, io, po) if return_indices else (o, d, rgb)
+
+
+class HostFeeder:
+    """Host -> device staging of training batches that live in pinned host memory (a DataLoader's output): batch n+1 is
+    copied on a dedicated copy stream into one of `depth` preallocated device slots while step n computes, so the upload
+    never sits between two kernels of the step.  `get(n)` returns the device tensors of batch n (the current stream is
+    made to wait for their copy) and keeps the copies of the following `depth - 2` batches in flight."""
+
+    def __init__(self, host_batches, device, depth=4, cycle=True):
+        self.host = host_batches
+        for b in host_batches:
+            for t in b:
+                assert t.is_pinned(), "HostFeeder wants pinned host tensors"
+        self.device = torch.device(device)
+        self.cycle = cycle
+        self.stream = torch.cuda.Stream(self.device)
+        self.slots = [tuple(torch.empty_like(t, device=self.device) for t in host_batches[0]) for _ in range(depth)]
+        self.ready = {}              # batch index -> (slot, event)
+        self.free_evt = [None] * depth   # last consumer of every slot
+        self.bytes_per_batch = sum(t.numel() * t.element_size() for t in host_batches[0])
+
+    def _issue(self, n):
+        if n in self.ready or (not self.cycle and n >= len(self.host)):
+            return
+        k = n % len(self.slots)
+        with torch.cuda.stream(self.stream):
+            if self.free_evt[k] is not None:
+                self.stream.wait_event(self.free_evt[k])       # the step that last read this slot has finished
+            for dst, src in zip(self.slots[k], self.host[n % len(self.host)]):
+                dst.copy_(src, non_blocking=True)
+            ev = torch.cuda.Event(); ev.record(self.stream)
+        self.ready[n] = (k, ev)
+
+    def get(self, n):
+        for j in range(len(self.slots) - 1):     # batch n for this step, n+1 for the march-ahead of this step, n+2 in flight
+            self._issue(n + j)
+        k, ev = self.ready.pop(n)
+        torch.cuda.current_stream(self.device).wait_event(ev)
+        return self.slots[k]
+
+    def peek(self, n):
+        """Device tensors of batch n (already issued by get(n - 1)) WITHOUT consuming them: for Trainer.step(next_rays=...).
+        The caller's side stream must wait for `event_of(n)` -- Engine.prefetch records its own dependency on the current
+        stream, so make the current stream wait first."""
+        self._issue(n)
+        k, ev = self.ready[n]
+        torch.cuda.current_stream(self.device).wait_event(ev)
+        return self.slots[k]
+
+    def done(self, n):
+        """Call after the step that consumed batch n has been enqueued: its slot may be overwritten once that work is done."""
+        k = n % len(self.slots)
+        ev = torch.cuda.Event(); ev.record(torch.cuda.current_stream(self.device))
+        self.free_evt[k] = ev
