@@ -334,6 +334,19 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* cfg, void* workspace, const void
                        const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
                        const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
                        const float* importance, int with_backward, int march_slot, rnb_stream_t stream);
+/* The same with the gate network taken off the critical path.  The gate forward (rnb_engine_gate) is needed only from
+ * the blend on, and the gate backward needs only the blend's output, so a caller may run both on a second stream next to
+ * the compositing kernels:  gate_ready_event (cudaEvent_t or NULL): the step's stream waits for it right before the
+ * blend;  blend_done_event (cudaEvent_t or NULL): recorded on the step's stream right after the blend;  skip_gate_bwd != 0:
+ * the caller runs rnb_engine_gate_bwd itself (after blend_done_event) and joins it before the optimizer. */
+int rnb_engine_fwd_bwd_ex(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* grads_f32,
+                          const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
+                          const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
+                          const float* importance, int with_backward, int march_slot, void* gate_ready_event,
+                          void* blend_done_event, int skip_gate_bwd, rnb_stream_t stream);
+/* Ray_Gate backward for the batch of the last rnb_engine_fwd_bwd[_ex]: accumulates into grads_f32[gate block]. */
+int rnb_engine_gate_bwd(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* grads_f32,
+                        rnb_stream_t stream);
 /* Marching depends on the rays and the occupancy bitfields only, not on the parameters: the samples of the NEXT
  * batch can be produced on a second stream while the current batch is in its field / backward kernels.
  * rnb_engine_march runs AABB + march + scan + expand for one batch into workspace slot `slot` (0 or 1);

@@ -514,10 +514,23 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
   return check_launch(what);
 }
 
-int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32,
+int rnb_engine_gate_bwd(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32, rnb_stream_t stream) {
+  const char* what = "rnb_engine_gate_bwd";
+  if (int rc = check_cfg(c, what)) return rc;
+  RNB_REQUIRE(workspace && params_f16 && grads_f32 && c->K > 1, what);
+  rnb_engine_layout L;
+  rnb_engine_layout_of(c, &L);
+  char* ws = (char*)workspace;
+  StageTimer tm(ST_GATE_BW, as_stream(stream));
+  return rnb_mlp_bwd(&kGateDesc, (const __half*)params_f16 + c->gate_off, ws + L.gate_in, ws + L.gate_hidden, ws + L.gate_logits,
+                     ws + L.gate_dlogits, c->n_rays, nullptr, grads_f32 + c->gate_off, 1.0f / c->loss_scale, stream);
+}
+
+int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32,
                        const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
                        const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
-                       const float* importance, int with_backward, int march_slot, rnb_stream_t stream) {
+                       const float* importance, int with_backward, int march_slot, void* gate_ready_event,
+                          void* blend_done_event, int skip_gate_bwd, rnb_stream_t stream) {
   const char* what = "rnb_engine_fwd_bwd";
   if (int rc = check_cfg(c, what)) return rc;
   RNB_REQUIRE(workspace && params_f16 && rays_o && rays_d && target_rgb && bg_host, what);
@@ -569,8 +582,12 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
   B.rgb = (float*)(ws + L.rgb); B.opacity = (float*)(ws + L.opacity); B.depth = (float*)(ws + L.depth);
   B.d_opacity = (float*)(ws + L.d_pass_opacity); B.d_depth = (float*)(ws + L.d_pass_depth); B.d_rgb = (float*)(ws + L.d_pass_rgb);
   B.dlogits = (__half*)(ws + L.gate_dlogits); B.loss = (float*)(ws + L.loss); B.with_backward = with_backward;
+  // the gate forward may have been issued on another stream (it is needed from here on only)
+  if (gate_ready_event != nullptr) RNB_CUDA(cudaStreamWaitEvent(st, (cudaEvent_t)gate_ready_event, 0), what);
   { StageTimer tm(ST_BLEND, st); eng_blend_loss_kernel<<<ceil_div(R, 256), 256, 0, st>>>(B); }
   if (int rc = check_launch(what)) return rc;
+  // ... and the gate backward may run on another stream next to the compositing backward: it needs the blend only
+  if (blend_done_event != nullptr) RNB_CUDA(cudaEventRecord((cudaEvent_t)blend_done_event, st), what);
   if (!with_backward) return RNB_OK;
   // 7. backward: composite, field, gate
   float* dsig = (float*)(ws + L.dsigmas); float* drgb = (float*)(ws + L.drgbs);
@@ -582,12 +599,16 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
   for (int i = 0; i < K; i++) { gg[i] = grads_f32 + c->geo_off[i]; gr[i] = grads_f32 + c->rgb_off[i]; }
   { StageTimer tm(ST_FIELD_BW, st);
   if (int rc = rnb_field_bwd(&P, &Sm, &Sv, rgb4, dsig, drgb, c->loss_scale, grads_f32 + c->table_off, gg, gr, stream)) return rc; }
-  if (K > 1) {
-    StageTimer tm(ST_GATE_BW, st);
-    if (int rc = rnb_mlp_bwd(&kGateDesc, p16 + c->gate_off, ws + L.gate_in, ws + L.gate_hidden, ws + L.gate_logits, ws + L.gate_dlogits,
-                             R, nullptr, grads_f32 + c->gate_off, 1.0f / c->loss_scale, stream)) return rc;
-  }
+  if (K > 1 && !skip_gate_bwd) return rnb_engine_gate_bwd(c, workspace, params_f16, grads_f32, stream);
   return RNB_OK;
+}
+
+int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* params_f16, float* grads_f32, const float* rays_o,
+                       const float* rays_d, const float* target_rgb, const float* noise, const uint8_t* const* bitfields,
+                       const float* bg_host, int64_t n_rays_global, const float* importance, int with_backward, int march_slot,
+                       rnb_stream_t stream) {
+  return rnb_engine_fwd_bwd_ex(c, workspace, params_f16, grads_f32, rays_o, rays_d, target_rgb, noise, bitfields, bg_host, n_rays_global,
+                               importance, with_backward, march_slot, nullptr, nullptr, 0, stream);
 }
 
 int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq, int64_t n,

@@ -12,6 +12,7 @@ There is no CPU path.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -147,6 +148,8 @@ class Engine:
         self.opt_step = 0
         # marching ahead (rnb_engine_march): the next batch's samples are produced on a side stream into the other slot
         self._march_stream = None
+        self._gate_stream = None        # gate forward / backward next to the compositing kernels (forward_backward)
+        self.overlap_gate = os.environ.get("RNB_NO_GATE_OVERLAP", "0") != "1"
         self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
         self._slot = 0                  # slot holding the samples of the batch last trained on
 
@@ -239,9 +242,25 @@ class Engine:
         self._slot = march_slot
         inline = hit is None
         st = stream_arg(self.device)
+        # The gate network is off the critical path where the data flow allows it (rnb_engine_fwd_bwd_ex): its forward is
+        # needed from the blend on and its backward needs only the blend, so both run on a second stream next to the
+        # compositing kernels.  With several ranks the forward stays in line: the importance all-reduce behind it is also
+        # the barrier that keeps this rank's field kernels behind every peer's parameter writes.
+        side_gate = self.K > 1 and self.overlap_gate
+        gate_evt = blend_evt = None
+        if side_gate and self._gate_stream is None:
+            self._gate_stream = torch.cuda.Stream(self.device)
+            self._blend_evt = torch.cuda.Event(); self._blend_evt.record(cur)      # materialise the handle once
         if self.K > 1:
-            call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
-            parallel.allreduce_sum_(self.importance)     # CV loss is non-linear in the batch: the importance must be global (8e)
+            if side_gate and self.world == 1:
+                ready = torch.cuda.Event(); ready.record(cur)
+                with torch.cuda.stream(self._gate_stream):
+                    self._gate_stream.wait_event(ready)
+                    call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, stream_arg(self.device))
+                    gate_evt = torch.cuda.Event(); gate_evt.record(self._gate_stream)
+            else:
+                call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
+                parallel.allreduce_sum_(self.importance)     # CV loss is non-linear in the batch: the importance must be global (8e)
         if next_rays is not None:
             self.prefetch(next_rays[0], next_rays[1])
         bfs = self.bitfields()
@@ -250,9 +269,21 @@ class Engine:
         if inline:
             call("rnb_engine_march", ctypes.byref(c), self.ws, rays_o, rays_d, noise, bf_arr, i32(march_slot), st)
             _lib.launch_count -= 3
-        call("rnb_engine_fwd_bwd", ctypes.byref(c), self.ws, self.flat16, self.grads if with_backward else None,
+        side_bwd = side_gate and with_backward
+        if side_bwd:
+            blend_evt = self._blend_evt
+        call("rnb_engine_fwd_bwd_ex", ctypes.byref(c), self.ws, self.flat16, self.grads if with_backward else None,
              rays_o, rays_d, target_rgb, noise, bf_arr, bg_arr, i64(self.n_rays * self.world),
-             self.importance if self.K > 1 else None, i32(1 if with_backward else 0), i32(march_slot), st)
+             self.importance if self.K > 1 else None, i32(1 if with_backward else 0), i32(march_slot),
+             ctypes.c_void_p(gate_evt.cuda_event) if gate_evt is not None else None,
+             ctypes.c_void_p(blend_evt.cuda_event) if blend_evt is not None else None, i32(1 if side_bwd else 0), st)
+        _lib.launch_count += 1 if (self.K > 1 and with_backward and not side_bwd) else 0
+        if side_bwd:
+            with torch.cuda.stream(self._gate_stream):
+                self._gate_stream.wait_event(blend_evt)
+                call("rnb_engine_gate_bwd", ctypes.byref(c), self.ws, self.flat16, self.grads, stream_arg(self.device))
+                joined = torch.cuda.Event(); joined.record(self._gate_stream)
+            cur.wait_event(joined)            # whatever follows on the step's stream (the optimizer) sees the gate gradients
 
     def adam_step(self, lr=None):
         self.opt_step += 1

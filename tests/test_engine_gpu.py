@@ -216,3 +216,30 @@ def test_empty_space_test_is_exact_on_sparse_grids(scale, esf):
         hit_any += int((ref_cnt > 0).sum())
         assert 0 < (ref_cnt > 0).sum()
     assert hit_any > 50
+
+
+def test_gate_on_side_stream_matches_in_line():
+    """The gate forward / backward issued on a second stream next to the compositing kernels (rnb_engine_fwd_bwd_ex) must
+    give the step of the in-line order: same outputs bit for bit, same gate gradients up to reduction order."""
+    from radnerf_b200.engine import Engine
+    scale, esf, K, n = 0.5, 0.0, 2, 2048
+    cam = syn.make_cameras(100, 1.5)
+    o, d, _, _ = syn.train_batch(cam, n, 21)
+    o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    target = torch.rand(n, 3, device="cuda")
+    torch.manual_seed(9)
+    noise = torch.rand(K, n, device="cuda")
+    out = []
+    for overlap in (False, True):
+        P, model, gate, bitfields = build(scale, K, 0.2)
+        eng = Engine(model, gate, n_rays=n, exp_step_factor=esf, lr=1e-2)
+        eng.overlap_gate = overlap
+        for _ in range(3):
+            loss = eng.step(o, d, target, noise=noise).clone()
+        torch.cuda.synchronize()
+        assert (eng._gate_stream is not None) == overlap
+        out.append((loss, eng.rgb.clone(), eng.gate_prob.clone(), eng.flat.clone()))
+    a, b = out
+    assert torch.allclose(a[0], b[0], rtol=1e-4, atol=1e-7)
+    assert float((a[1] - b[1]).abs().max()) < 1e-3 and float((a[2] - b[2]).abs().max()) < 1e-3
+    assert float(((a[3] - b[3]).abs() > 1e-3).float().mean()) < 0.01
