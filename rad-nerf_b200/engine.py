@@ -244,19 +244,21 @@ class Engine:
         st = stream_arg(self.device)
         # The gate network is off the critical path where the data flow allows it (rnb_engine_fwd_bwd_ex): its forward is
         # needed from the blend on and its backward needs only the blend, so both run on a second stream next to the
-        # compositing kernels.  With several ranks the forward stays in line: the importance all-reduce behind it is also
-        # the barrier that keeps this rank's field kernels behind every peer's parameter writes.
+        # compositing kernels.  (With several ranks and the in-line order the importance all-reduce doubles as the barrier
+        # that keeps this rank's field kernels behind every peer's parameter writes; with the gate on the side stream
+        # adam_step issues that barrier itself.)
         side_gate = self.K > 1 and self.overlap_gate
         gate_evt = blend_evt = None
         if side_gate and self._gate_stream is None:
             self._gate_stream = torch.cuda.Stream(self.device)
             self._blend_evt = torch.cuda.Event(); self._blend_evt.record(cur)      # materialise the handle once
         if self.K > 1:
-            if side_gate and self.world == 1:
+            if side_gate:
                 ready = torch.cuda.Event(); ready.record(cur)
                 with torch.cuda.stream(self._gate_stream):
                     self._gate_stream.wait_event(ready)
                     call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, stream_arg(self.device))
+                    parallel.allreduce_sum_(self.importance)
                     gate_evt = torch.cuda.Event(); gate_evt.record(self._gate_stream)
             else:
                 call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
@@ -300,7 +302,7 @@ class Engine:
                  self._peer_p.pointer_array(), self.flat, self.exp_avg, self.exp_avg_sq, i64(self.n_params), i64(n_sharded),
                  prev.local, f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps),
                  i64(self.opt_step), f32(1.0), stream_arg(self.device))
-            if self.K == 1:
+            if self.K == 1 or self.overlap_gate:
                 parallel.stream_barrier(self.device)
             self._g ^= 1
             self.grads = self._peer_g[self._g].local.view(torch.float32)      # (cleared by the kernel of the previous step)
