@@ -286,14 +286,23 @@ def run_product(args):
         # device->host read of every step's loss: an asynchronous copy into pinned memory, consumed one step later so that
         # the host keeps launching ahead (what a training loop that logs its loss does); the last ones are drained below
         k = s % 4
-        loss_pin[k].copy_(loss_vec, non_blocking=True)
-        ev = torch.cuda.Event(); ev.record(); loss_evt[k] = ev
+        if rb_stream is None:
+            loss_pin[k].copy_(loss_vec, non_blocking=True)
+            ev = torch.cuda.Event(); ev.record(); loss_evt[k] = ev
+        else:
+            # the copy engine's turn sits on its own stream: the step's stream never waits for a DMA between two kernels
+            done = torch.cuda.Event(); done.record()
+            with torch.cuda.stream(rb_stream):
+                rb_stream.wait_event(done)
+                loss_pin[k].copy_(loss_vec, non_blocking=True)
+                ev = torch.cuda.Event(); ev.record(rb_stream); loss_evt[k] = ev
         j = (s - 1) % 4
         if s > 0 and loss_evt[j] is not None:
             loss_evt[j].synchronize()
             losses.append(float(loss_pin[j][0]))
 
     feeder = None
+    rb_stream = torch.cuda.Stream() if os.environ.get("RNB_E2E_INLINE_READBACK") != "1" else None
 
     def e2e_step(s):
         # every step uploads ONE batch from pinned host memory and reads the step's loss back.  The upload goes through
@@ -301,6 +310,9 @@ def run_product(args):
         # also the batch whose rays are marched on the side stream), so the copy never sits between two kernels
         nonlocal feeder
         flush_l2()
+        if rb_stream is not None and s > 0 and loss_evt[(s - 1) % 4] is not None:
+            # the next step clears the loss vector: order it behind the previous step's read-back (long finished by now)
+            torch.cuda.current_stream().wait_event(loss_evt[(s - 1) % 4])
         if feeder is None:
             from radnerf_b200.data import HostFeeder
             feeder = HostFeeder(host, f"cuda:{local}", depth=4)
@@ -335,7 +347,9 @@ def run_product(args):
     launches = _lib.launch_count - n0
     clk = clocks.stop()
     ms_step = ms / args.steps - flush_ms
-    e2e_ms = timed(e2e_step, args.steps) / args.steps - flush_ms
+    for s in range(args.warmup):         # untimed: feeder slots, copy / read-back streams and pinned buffers come up here
+        e2e_step(s)
+    e2e_ms = timed(lambda s: e2e_step(s + args.warmup), args.steps) / args.steps - flush_ms
     # per-stage device time of the same steps (separate pass: CUDA events around every stage of the fused step)
     stage_ms = {}
     if tr.engine is not None:

@@ -23,16 +23,44 @@ __device__ __forceinline__ void load_rgb(const void* __restrict__ rgbs, int64_t 
 // Serial transmittance over the 32 lanes.  On entry T_in = transmittance before lane 0's
 // sample (warp-uniform); returns this lane's transmittance BEFORE its sample and updates
 // T_in to the value after lane 31's sample.
+// Every lane replays the chain ((T_in * om_0) * om_1) * ... itself, stopping at its own index, from a
+// shared-memory copy of the 32 factors read as eight broadcast 16-byte loads: the loop-carried dependency is the
+// 32 multiplies alone (~130 cycles per chunk).  The earlier form -- one SHFL per factor feeding one running
+// product -- compiled to SHFL -> FMUL pairs through a single register, ~1000 cycles per chunk, and the longest
+// ray of the batch (up to 32 chunks) set the duration of the whole compositing kernel.
 __device__ __forceinline__ float serial_T(float one_minus_a, float& T_in, int lane) {
-  float run = T_in, mine = T_in;
+  __shared__ __align__(16) float s_om[32][32];      // [warp of the CTA][lane]
+  float* row = s_om[threadIdx.x >> 5];
+  __syncwarp();                                     // the previous chunk's reads are complete
+  row[lane] = one_minus_a;
+  __syncwarp();
+  float mine = T_in;
 #pragma unroll
-  for (int j = 0; j < 32; j++) {
-    const float om = __shfl_sync(kFullMask, one_minus_a, j);
-    if (lane == j) mine = run;
-    run = __fmul_rn(run, om);
+  for (int q = 0; q < 8; q++) {
+    const float4 v = reinterpret_cast<const float4*>(row)[q];
+    if (4 * q + 0 < lane) mine = __fmul_rn(mine, v.x);
+    if (4 * q + 1 < lane) mine = __fmul_rn(mine, v.y);
+    if (4 * q + 2 < lane) mine = __fmul_rn(mine, v.z);
+    if (4 * q + 3 < lane) mine = __fmul_rn(mine, v.w);
   }
-  T_in = run;
+  T_in = __shfl_sync(kFullMask, __fmul_rn(mine, one_minus_a), 31);
   return mine;
+}
+
+// One lane's sample of a chunk (zeros past the end of the segment).
+struct SampleIn { float sigma, dl, r, g, b, t; };
+template <bool kHalf4>
+__device__ __forceinline__ SampleIn load_sample(const float* __restrict__ sigmas, const void* __restrict__ rgbs,
+                                                const float* __restrict__ deltas, const float* __restrict__ ts,
+                                                int64_t start, int k, int N) {
+  SampleIn v = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (k < N) {
+    const int64_t s = start + k;
+    v.sigma = ld_stream_f32(sigmas + s); v.dl = ld_stream_f32(deltas + s);
+    load_rgb<kHalf4>(rgbs, s, v.r, v.g, v.b);
+    v.t = ld_stream_f32(ts + s);
+  }
+  return v;
 }
 
 struct RayAccum { float R, G, B, D, O; int total; };
@@ -47,16 +75,16 @@ __device__ __forceinline__ RayAccum composite_fw_segment(const float* __restrict
   float T = 1.0f, R = 0.f, G = 0.f, B = 0.f, D = 0.f, O = 0.f;
   int total = N;
   int base = 0;
+  // The chunk loop is software-pipelined: the loads of chunk c+1 are issued before the serial chain of chunk c,
+  // so a long ray pays one memory latency, not one per 32 samples (the longest ray sets the kernel's duration).
+  SampleIn cur = load_sample<kHalf4>(sigmas, rgbs, deltas, ts, start, lane, N);
   for (; base < N; base += 32) {
+    const SampleIn nxt = load_sample<kHalf4>(sigmas, rgbs, deltas, ts, start, base + 32 + lane, N);
     const int k = base + lane;
     const bool valid = k < N;
     const int64_t s = start + k;
-    float a = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, tt = 0.f;
-    if (valid) {
-      a = 1.0f - __expf(-ld_stream_f32(sigmas + s) * ld_stream_f32(deltas + s));
-      load_rgb<kHalf4>(rgbs, s, cr, cg, cb);
-      tt = ld_stream_f32(ts + s);
-    }
+    const float a = valid ? 1.0f - __expf(-cur.sigma * cur.dl) : 0.f;
+    const float cr = cur.r, cg = cur.g, cb = cur.b, tt = cur.t;
     const float om = 1.0f - a;
     const float Tb = serial_T(om, T, lane);
     const float Ta = __fmul_rn(Tb, om);
@@ -66,6 +94,7 @@ __device__ __forceinline__ RayAccum composite_fw_segment(const float* __restrict
     if (valid) ws[s] = w;
     R = fmaf(w, cr, R); G = fmaf(w, cg, G); B = fmaf(w, cb, B); D = fmaf(w, tt, D); O += w;
     if (term) { total = base + first; base += 32; break; }
+    cur = nxt;
   }
   // samples behind the terminating chunk keep ws = 0 (reference: zero-initialised, Q8)
   for (int k = base + lane; k < N; k += 32) ws[start + k] = 0.f;
@@ -96,18 +125,20 @@ __device__ __forceinline__ void composite_bw_segment(const RayGrad q, const floa
   }
   float T = 1.0f, r = 0.f, g = 0.f, b = 0.f, d = 0.f, wsrun = 0.f;  // carries (warp-uniform)
   int base = 0;
+  // software-pipelined like the forward loop: chunk c+1 is in flight while chunk c's chain and scans run
+  SampleIn cur = load_sample<kHalf4>(sigmas, rgbs, deltas, ts, start, lane, N);
+  float cgw = 0.f, cwv = 0.f;
+  if (dL_dws && lane < N) { cgw = ld_stream_f32(dL_dws + start + lane); cwv = ld_stream_f32(ws + start + lane); }
   for (; base < N; base += 32) {
+    const int kn = base + 32 + lane;
+    const SampleIn nxt = load_sample<kHalf4>(sigmas, rgbs, deltas, ts, start, kn, N);
+    float ngw = 0.f, nwv = 0.f;
+    if (dL_dws && kn < N) { ngw = ld_stream_f32(dL_dws + start + kn); nwv = ld_stream_f32(ws + start + kn); }
     const int k = base + lane;
     const bool valid = k < N;
     const int64_t s = start + k;
-    float a = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, tt = 0.f, dl = 0.f, gw = 0.f, wv = 0.f;
-    if (valid) {
-      dl = ld_stream_f32(deltas + s);
-      a = 1.0f - __expf(-ld_stream_f32(sigmas + s) * dl);
-      load_rgb<kHalf4>(rgbs, s, cr, cg, cb);
-      tt = ld_stream_f32(ts + s);
-      if (dL_dws) { gw = ld_stream_f32(dL_dws + s); wv = ld_stream_f32(ws + s); }
-    }
+    const float dl = cur.dl, cr = cur.r, cg = cur.g, cb = cur.b, tt = cur.t, gw = cgw, wv = cwv;
+    const float a = valid ? 1.0f - __expf(-cur.sigma * dl) : 0.f;
     const float om = 1.0f - a;
     const float Tb = serial_T(om, T, lane);
     const float Ta = __fmul_rn(Tb, om);
@@ -131,6 +162,7 @@ __device__ __forceinline__ void composite_bw_segment(const RayGrad q, const floa
     if (term) { base += 32; break; }
     r = __shfl_sync(kFullMask, pr, 31); g = __shfl_sync(kFullMask, pg, 31); b = __shfl_sync(kFullMask, pb, 31);
     d = __shfl_sync(kFullMask, pd, 31); wsrun = __shfl_sync(kFullMask, pw, 31);
+    cur = nxt; cgw = ngw; cwv = nwv;
   }
   for (int k = base + lane; k < N; k += 32) {
     const int64_t s = start + k;
