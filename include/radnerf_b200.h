@@ -462,6 +462,9 @@ int rnb_batch_rays(const float* directions, const float* poses, const float* ima
  * counts since the previous read (arrays of n >= 11 entries) and clears them. */
 int rnb_engine_profile(int enable);
 int rnb_engine_profile_read(double* ms, int32_t* calls, int n);
+/* The same records as a timeline (issue order): stage index, start and end in ms relative to the first record; the
+ * events of the step's side streams share the device clock, so overlap and gaps between stages are visible. */
+int rnb_engine_profile_timeline(int32_t* stage, double* start_ms, double* end_ms, int n_max, int32_t* n_out);
 
 /* Selects the implementation behind rnb_field_fwd / rnb_field_bwd: 1 = tcgen05 + TMEM kernels
  * (csrc/field_tc.cu, default where available), 0 = mma.sync register-chained kernels (csrc/field.cu).

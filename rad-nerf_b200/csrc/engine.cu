@@ -570,9 +570,6 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   { StageTimer tm(ST_FIELD_FWD, st); if (int rc = rnb_field_fwd(&P, &Sm, with_backward ? &Sv : nullptr, sigmas, rgb4, stream)) return rc; }
   // 5. composite, 6. blend + loss + gradient seeds
   float* p_op = (float*)(ws + L.pass_opacity); float* p_de = (float*)(ws + L.pass_depth); float* p_rgb = (float*)(ws + L.pass_rgb);
-  { StageTimer tm(ST_COMP_FW, st);
-  eng_composite_fw_kernel<<<ray_grid, 256, 0, st>>>(sigmas, rgb4, deltas, ts, counts, starts, c->T_threshold, R, S, wsamp, p_op, p_de, p_rgb,
-                                                    (int32_t*)(ws + L.pass_total)); }
   BlendArgs B;
   B.n_rays = R; B.K = K; B.inv_rays_global = 1.0f / (float)n_rays_global;
   B.lambda_opacity = c->lambda_opacity; B.lambda_cv = c->lambda_cv; B.lambda_dm = c->lambda_dm; B.gs = c->loss_scale;
@@ -582,6 +579,10 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   B.rgb = (float*)(ws + L.rgb); B.opacity = (float*)(ws + L.opacity); B.depth = (float*)(ws + L.depth);
   B.d_opacity = (float*)(ws + L.d_pass_opacity); B.d_depth = (float*)(ws + L.d_pass_depth); B.d_rgb = (float*)(ws + L.d_pass_rgb);
   B.dlogits = (__half*)(ws + L.gate_dlogits); B.loss = (float*)(ws + L.loss); B.with_backward = with_backward;
+  float* dsig = (float*)(ws + L.dsigmas); float* drgb = (float*)(ws + L.drgbs);
+  { StageTimer tm(ST_COMP_FW, st);
+  eng_composite_fw_kernel<<<ray_grid, 256, 0, st>>>(sigmas, rgb4, deltas, ts, counts, starts, c->T_threshold, R, S, wsamp, p_op, p_de, p_rgb,
+                                                    (int32_t*)(ws + L.pass_total)); }
   // the gate forward may have been issued on another stream (it is needed from here on only)
   if (gate_ready_event != nullptr) RNB_CUDA(cudaStreamWaitEvent(st, (cudaEvent_t)gate_ready_event, 0), what);
   { StageTimer tm(ST_BLEND, st); eng_blend_loss_kernel<<<ceil_div(R, 256), 256, 0, st>>>(B); }
@@ -590,7 +591,6 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   if (blend_done_event != nullptr) RNB_CUDA(cudaEventRecord((cudaEvent_t)blend_done_event, st), what);
   if (!with_backward) return RNB_OK;
   // 7. backward: composite, field, gate
-  float* dsig = (float*)(ws + L.dsigmas); float* drgb = (float*)(ws + L.drgbs);
   { StageTimer tm(ST_COMP_BW, st);
   eng_composite_bw_kernel<<<ray_grid, 256, 0, st>>>(sigmas, rgb4, deltas, ts, counts, starts, c->T_threshold, R, S, p_op, p_de, p_rgb,
                                                     B.d_opacity, B.d_depth, B.d_rgb, dsig, drgb); }
@@ -620,7 +620,7 @@ int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float
   const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
   const float step_size = (float)(lr / bc1), inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
   int64_t blocks = (n / 4 + 255) / 256;
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;      // (a single resident wave, 5 blocks per SM, measured 3 % slower)
   if (blocks < 1) blocks = 1;
   StageTimer tm(ST_ADAM, as_stream(stream));
   eng_adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(params_f32, (__half*)params_f16, grads_f32, exp_avg, exp_avg_sq, n, step_size,
@@ -646,6 +646,27 @@ int rnb_engine_profile_read(double* ms, int32_t* calls, int n) {
     cudaEventDestroy(r.a); cudaEventDestroy(r.b);
   }
   g_prof.clear();
+  return RNB_OK;
+}
+
+/* Timeline of the recorded stages since the last read: stage id, start and end in milliseconds relative to the first
+ * record (events of different streams share the device clock), in issue order.  Returns the records through *n_out
+ * (at most n_max), synchronises and clears like rnb_engine_profile_read. */
+int rnb_engine_profile_timeline(int32_t* stage, double* start_ms, double* end_ms, int n_max, int32_t* n_out) {
+  const char* what = "rnb_engine_profile_timeline";
+  RNB_REQUIRE(stage && start_ms && end_ms && n_out && n_max >= 0, what);
+  int n = 0;
+  cudaEvent_t origin = g_prof.empty() ? nullptr : g_prof.front().a;
+  for (auto& r : g_prof) cudaEventSynchronize(r.b);
+  for (auto& r : g_prof) {
+    float t0 = 0.f, t1 = 0.f;
+    if (n < n_max && cudaEventElapsedTime(&t0, origin, r.a) == cudaSuccess && cudaEventElapsedTime(&t1, origin, r.b) == cudaSuccess) {
+      stage[n] = r.stage; start_ms[n] = t0; end_ms[n] = t1; n++;
+    }
+  }
+  for (auto& r : g_prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  g_prof.clear();
+  *n_out = n;
   return RNB_OK;
 }
 

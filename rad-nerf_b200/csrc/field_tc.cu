@@ -178,6 +178,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
   uint64_t* bar = bars + wg;
   uint32_t phase = 0;
   const int K = A.K;
+  int64_t tiles_before = 0;
   for (int pass = 0; pass < K; pass++) {
     const int64_t base = __ldg(A.seg + pass);
     int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
@@ -198,7 +199,13 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
     __syncthreads();
     // The sample -> ray -> origin/direction lookups are two dependent global loads in front of the first gather: they are
     // issued one tile ahead (while this tile is in its layer chain) and carried in registers.
-    const int64_t tile0 = (int64_t)blockIdx.x * kWG + wg, tstride = (int64_t)gridDim.x * kWG;
+    // Tiles go round-robin over the grid's warpgroups; each pass starts where the previous one stopped, so the
+    // warpgroups that took the odd tile of one pass are not the ones that take it in the next (with a fixed start, the
+    // first CTAs carried ceil(tiles / warpgroups) in EVERY pass and set the kernel's duration).
+    const int64_t tstride = (int64_t)gridDim.x * kWG;
+    int64_t tile0 = (int64_t)blockIdx.x * kWG + wg - tiles_before % tstride;
+    if (tile0 < 0) tile0 += tstride;
+    tiles_before += n_tiles;
     float nt = 0.f, nox = 0.f, noy = 0.f, noz = 0.f, ndx = 0.f, ndy = 0.f, ndz = 0.f;
     if (tile0 < n_tiles && base + tile0 * kRows + row < pass_end) {
       const int64_t s0 = base + tile0 * kRows + row;
@@ -597,6 +604,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
   uint32_t in_buf[kWGB] = {0, 0, 0, 0};    // issuer-side: which saved-input buffer the next step of warpgroup g reads
   uint32_t ph_done = 0;                    // warpgroup-side parity
   uint32_t q_load = 0;                     // warpgroup-side: saved-input tiles consumed so far (buffer = q & 1, parity = (q >> 1) & 1)
+  int64_t tiles_before = 0;
   for (int pass = 0; pass < K; pass++) {
     const int64_t base = __ldg(A.seg + pass);
     int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
@@ -615,8 +623,14 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
     }
     tc::fence_async_smem();
     __syncthreads();
-    const int64_t first_tile = (int64_t)blockIdx.x * kWGB;
+    // round-robin over the grid's warpgroups, each pass continuing where the previous one stopped (see the forward kernel)
     const int64_t tile_stride = (int64_t)gridDim.x * kWGB;
+    const int64_t rot = tiles_before % tile_stride;
+    tiles_before += n_tiles;
+    auto wg_first = [&](int g) -> int64_t {
+      const int64_t t = (int64_t)blockIdx.x * kWGB + g - rot;
+      return t < 0 ? t + tile_stride : t;
+    };
     if (is_issuer) {
       // ---------------- issuer warp: every MMA of the CTA, in arrival order ----------------
       if (lane == 0) {
@@ -624,7 +638,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
         int remaining = 0;
 #pragma unroll
         for (int g = 0; g < kWGB; g++) {
-          const int64_t t0 = first_tile + g;
+          const int64_t t0 = wg_first(g);
           left[g] = t0 < n_tiles ? (n_tiles - t0 + tile_stride - 1) / tile_stride : 0;
           step[g] = 0;
           remaining += (int)left[g];
@@ -676,7 +690,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
       const uint32_t inb_s = tc::smem_u32(inb);
       uint64_t* ld = loaded + 2 * wg;
       const uint32_t tmem_row = tmem + kColD + wg * 64 + ((uint32_t)((warp & 3) * 32) << 16);
-      const int64_t t0 = first_tile + wg;
+      const int64_t t0 = wg_first(wg);
       const int64_t my_tiles = t0 < n_tiles ? (n_tiles - t0 + tile_stride - 1) / tile_stride : 0;
       // Saved-input tiles arrive by bulk copy in the order the layers consume them: per tile h2, h1, rgb_in, geo_h, enc.
       // The forward kernel stored them in the operand-tile layout, so they are MMA operands as they land.  Load number
@@ -813,7 +827,10 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    if (warp < 4 && first_tile < n_tiles) {
+    bool cta_had_tiles = false;
+#pragma unroll
+    for (int g = 0; g < kWGB; g++) cta_had_tiles |= wg_first(g) < n_tiles;
+    if (warp < 4 && cta_had_tiles) {
       float* gg = G.geo[pass]; float* gr = G.rgb[pass];
       tc_flush_wgrad<32>(tmem + kColWg1, 64, gg, inv_gs, warp, lane);
       tc_flush_wgrad<64>(tmem + kColWg2, 32, gg + 64 * 32, inv_gs, warp, lane);

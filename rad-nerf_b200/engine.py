@@ -250,7 +250,7 @@ class Engine:
         side_gate = self.K > 1 and self.overlap_gate
         gate_evt = blend_evt = None
         if side_gate and self._gate_stream is None:
-            self._gate_stream = torch.cuda.Stream(self.device)
+            self._gate_stream = torch.cuda.Stream(self.device, priority=-1)      # ahead of the marcher's stream: the blend waits for it
             self._blend_evt = torch.cuda.Event(); self._blend_evt.record(cur)      # materialise the handle once
         if self.K > 1:
             if side_gate:
