@@ -793,15 +793,21 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
             *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, c)) =
                 make_uint4(pack2h(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])), pack2h(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3])),
                            pack2h(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])), pack2h(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7])));
+          // the per-level constants are indexed loads from the parameter bank (~100+ cycles each, and the loop is rolled):
+          // level l + 1's are fetched while level l is processed
+          float sc_n = A.g.scale[0];
+          uint32_t res_n = A.g.res[0], off_n = A.g.offset[0], end_n = A.g.offset[1];
 #pragma unroll 1
           for (int l = 0; l < 16; l++) {
-            const uint32_t off = A.g.offset[l];
-            const LevelCorners L = level_corners(x, y, z, A.g.scale[l], A.g.res[l], A.g.offset[l + 1] - off);
+            const uint32_t off = off_n, res_l = res_n, end_l = end_n;
+            const float sc_l = sc_n;
+            if (l < 15) { sc_n = A.g.scale[l + 1]; res_n = A.g.res[l + 1]; off_n = end_l; end_n = A.g.offset[l + 2]; }
+            const LevelCorners L = level_corners(x, y, z, sc_l, res_l, end_l - off);
             const float2 d = __half22float2(*reinterpret_cast<const __half2*>(dzb + tc::tile_chunk_off(kRows, row, l >> 2) + (l & 3) * 4));
             const float d0 = d.x * inv_gs, d1 = d.y * inv_gs;
             float* gl = grad_table + 2 * (size_t)off;
             if (l < n_aggregate_levels) {   // warp-uniform
-              if (A.g.res[l] <= (uint32_t)agg_long_res) scatter_level_aggregated<5>(gl, L, d0, d1, valid);
+              if (res_l <= (uint32_t)agg_long_res) scatter_level_aggregated<5>(gl, L, d0, d1, valid);
               else scatter_level_aggregated<3>(gl, L, d0, d1, valid);
             } else if (valid) {
               // x-neighbour corners that share an aligned pair of entries (see tc_encode_level) take ONE 16-byte reduction
