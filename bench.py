@@ -148,7 +148,7 @@ def measured_peaks():
 #   + 52 B/ray; composite bw 48 B/sample + 64 B/ray; field bwd = encode bwd 76 B/sample; adam 28 B/param.
 #   flops: MLP fwd 18 944 FLOP/sample (unpadded), bwd 37 888 FLOP/sample; gate 25 344 + 128 K FLOP/ray.
 STAGES = ["gate", "march", "scan", "expand", "field_fwd", "composite_fw", "blend_loss", "composite_bw", "field_bwd",
-          "gate_bwd", "adam"]
+          "gate_bwd", "adam", "barrier"]
 STAGE_BYTES = {
     "march": lambda N, KR, P: 60 * KR + 20 * N,
     "expand": lambda N, KR, P: 12 * N,

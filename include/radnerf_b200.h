@@ -458,10 +458,14 @@ int rnb_batch_rays(const float* directions, const float* poses, const float* ima
 
 /* Optional per-stage device timing of the fused step (CUDA events around every stage; off by default).
  * Stage order: gate, march, scan, expand, field_fwd, composite_fw, blend_loss, composite_bw, field_bwd,
- * gate_bwd, adam.  rnb_engine_profile_read synchronises, returns the accumulated milliseconds and call
- * counts since the previous read (arrays of n >= 11 entries) and clears them. */
+ * gate_bwd, adam, barrier (caller-recorded).  rnb_engine_profile_read synchronises, returns the accumulated
+ * milliseconds and call counts since the previous read (arrays of n >= 12 entries) and clears them. */
 int rnb_engine_profile(int enable);
 int rnb_engine_profile_read(double* ms, int32_t* calls, int n);
+/* Caller-recorded spans for work the library does not launch itself (collectives issued by the host side, the
+ * peer-memory optimizer): stage 11 = "barrier", 10 = "adam".  begin returns a handle, or -1 when profiling is off. */
+int rnb_engine_profile_span_begin(int stage, rnb_stream_t stream);
+int rnb_engine_profile_span_end(int handle, rnb_stream_t stream);
 /* The same records as a timeline (issue order): stage index, start and end in ms relative to the first record; the
  * events of the step's side streams share the device clock, so overlap and gaps between stages are visible. */
 int rnb_engine_profile_timeline(int32_t* stage, double* start_ms, double* end_ms, int n_max, int32_t* n_out);

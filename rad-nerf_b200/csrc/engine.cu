@@ -382,7 +382,7 @@ using namespace rnb;
 // ---- optional per-stage device timing (bench.py's roofline leg; off by default) -------------------------
 #include <vector>
 namespace {
-enum Stage { ST_GATE = 0, ST_MARCH, ST_SCAN, ST_EXPAND, ST_FIELD_FWD, ST_COMP_FW, ST_BLEND, ST_COMP_BW, ST_FIELD_BW, ST_GATE_BW, ST_ADAM, ST_COUNT };
+enum Stage { ST_GATE = 0, ST_MARCH, ST_SCAN, ST_EXPAND, ST_FIELD_FWD, ST_COMP_FW, ST_BLEND, ST_COMP_BW, ST_FIELD_BW, ST_GATE_BW, ST_ADAM, ST_BARRIER, ST_COUNT };
 struct ProfRec { int stage; cudaEvent_t a, b; };
 std::vector<ProfRec> g_prof;
 bool g_prof_on = false;
@@ -646,6 +646,23 @@ int rnb_engine_profile_read(double* ms, int32_t* calls, int n) {
     cudaEventDestroy(r.a); cudaEventDestroy(r.b);
   }
   g_prof.clear();
+  return RNB_OK;
+}
+
+/* Spans recorded by the caller around work the library does not launch itself (the host side's collectives, the
+ * peer-memory optimizer): begin returns a handle (>= 0) or -1 when profiling is off; end records the closing event. */
+int rnb_engine_profile_span_begin(int stage, rnb_stream_t stream) {
+  if (!g_prof_on || stage < 0 || stage >= ST_COUNT) return -1;
+  ProfRec r; r.stage = stage;
+  cudaEventCreate(&r.a); cudaEventCreate(&r.b);
+  cudaEventRecord(r.a, as_stream(stream));
+  g_prof.push_back(r);
+  return (int)g_prof.size() - 1;
+}
+
+int rnb_engine_profile_span_end(int handle, rnb_stream_t stream) {
+  if (handle < 0 || handle >= (int)g_prof.size()) return RNB_OK;
+  cudaEventRecord(g_prof[handle].b, as_stream(stream));
   return RNB_OK;
 }
 

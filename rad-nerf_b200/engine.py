@@ -61,6 +61,19 @@ class _GridLayout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int64) for n in _GRID_LAYOUT_FIELDS]
 
 
+class _Span:
+    """Caller-recorded profile span (rnb_engine_profile_span_*): a no-op unless rnb_engine_profile(1) is on."""
+    ADAM, BARRIER = 10, 11
+
+    def __init__(self, stage, device):
+        self.device = device
+        self.h = _lib.lib().rnb_engine_profile_span_begin(i32(stage), stream_arg(device))
+
+    def end(self):
+        if self.h >= 0:
+            _lib.lib().rnb_engine_profile_span_end(i32(self.h), stream_arg(self.device))
+
+
 class Engine:
     def __init__(self, model, gate=None, n_rays=8192, exp_step_factor=0.0, samples_per_ray=128, max_samples=1024,
                  T_threshold=1e-4, near_distance=0.01, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
@@ -258,7 +271,8 @@ class Engine:
                 with torch.cuda.stream(self._gate_stream):
                     self._gate_stream.wait_event(ready)
                     call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, stream_arg(self.device))
-                    parallel.allreduce_sum_(self.importance)
+                    if self.world > 1:
+                        sp = _Span(_Span.BARRIER, self.device); parallel.allreduce_sum_(self.importance); sp.end()
                     gate_evt = torch.cuda.Event(); gate_evt.record(self._gate_stream)
             else:
                 call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
@@ -295,15 +309,17 @@ class Engine:
             # cleared.  The stream barrier in front orders it after every rank's backward.  Behind it, the next step's gate
             # forward touches only this rank's own gate replica and the importance all-reduce that follows it completes only
             # once every rank has left this kernel -- for K = 1 there is no such all-reduce, so a second barrier is issued.
-            parallel.stream_barrier(self.device)
+            sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             cur, prev = self._peer_g[self._g], self._peer_g[self._g ^ 1]
             n_sharded = self.offsets["gate"] if self.K > 1 else self.n_params
+            sp = _Span(_Span.ADAM, self.device)
             call("rnb_engine_adam_sharded", i32(parallel.rank()), i32(self.world), cur.pointer_array(),
                  self._peer_p.pointer_array(), self.flat, self.exp_avg, self.exp_avg_sq, i64(self.n_params), i64(n_sharded),
                  prev.local, f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps),
                  i64(self.opt_step), f32(1.0), stream_arg(self.device))
+            sp.end()
             if self.K == 1 or self.overlap_gate:
-                parallel.stream_barrier(self.device)
+                sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             self._g ^= 1
             self.grads = self._peer_g[self._g].local.view(torch.float32)      # (cleared by the kernel of the previous step)
             self._master_stale = True

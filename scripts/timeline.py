@@ -13,12 +13,18 @@ from bench import BATCH, STAGES, make_batches, scene_bitfields, workload  # noqa
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "radnerf_tat_k2"
     syn, w = workload(name)
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:       # under torchrun: the multi-rank step (peer-memory optimizer, stream barriers) on rank 0's clock
+        import torch.distributed as dist
+        opts = dist.ProcessGroupNCCL.Options(); opts.is_high_priority_stream = True
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
     from radnerf_b200 import _lib
     from radnerf_b200.trainer import Trainer
     lib = _lib.lib()
-    tr = Trainer(scale=w["scale"], K=w["K"], freeze_occupancy=True, device="cuda:0", engine=True, batch_rays=BATCH)
+    tr = Trainer(scale=w["scale"], K=w["K"], freeze_occupancy=True, device=f"cuda:{local}", engine=True, batch_rays=BATCH)
     tr.set_occupancy(scene_bitfields(syn, w))
-    dev = [tuple(torch.from_numpy(a).cuda() for a in b) for b in make_batches(syn, w, 0)]
+    dev = [tuple(torch.from_numpy(a).cuda() for a in b) for b in make_batches(syn, w, rank)]
     flush = torch.empty(256 * 1024 * 1024 // 4, device="cuda")
     torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
 
@@ -36,6 +42,9 @@ def main():
     st = (ctypes.c_int32 * n_max)(); t0 = (ctypes.c_double * n_max)(); t1 = (ctypes.c_double * n_max)(); n = ctypes.c_int32(0)
     lib.rnb_engine_profile_timeline(st, t0, t1, n_max, ctypes.byref(n))
     lib.rnb_engine_profile(0)
+    if rank != 0:
+        dist.destroy_process_group()
+        return
     recs = sorted((t0[i], t1[i], STAGES[st[i]]) for i in range(n.value))
     # print the last full step: from the last field_fwd's predecessor gate to its adam
     adams = [r for r in recs if r[2] == "adam"]
@@ -45,6 +54,8 @@ def main():
     for a, b, nm in recs:
         if a >= lo - 1e-6:
             print(f"{nm:14s} {1e3 * (a - lo):9.1f} {1e3 * (b - lo):9.1f} {1e3 * (b - a):8.1f}")
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
