@@ -171,10 +171,14 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
   if (int rc = rnb_adam_shard_bounds(n_sharded, rank, world, &lo, &hi)) return rc;
   const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
   const float step_size = (float)(lr / bc1), inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  // instantiation width: the smallest of 2 / 4 / 8 peers that holds `world` (RNB_PEER_MIN_WIDTH: test hook that runs the
+  // wider instantiations on a box with fewer GPUs, tests/test_multi_gpu.py)
+  int width = world <= 2 ? 2 : world <= 4 ? 4 : RNB_MAX_PEERS;
+  if (const char* e = getenv("RNB_PEER_MIN_WIDTH")) { const int w = atoi(e); if (w > width && w <= RNB_MAX_PEERS) width = w > 4 ? RNB_MAX_PEERS : 4; }
   // one resident wave of grid-stride blocks (the pipelined loop wants every thread to start at once)
   int per_sm = 0;
-  cudaError_t oe = world <= 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_sharded_kernel<2>, 256, 0)
-                 : world <= 4 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_sharded_kernel<4>, 256, 0)
+  cudaError_t oe = width == 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_sharded_kernel<2>, 256, 0)
+                 : width == 4 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_sharded_kernel<4>, 256, 0)
                               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_sharded_kernel<RNB_MAX_PEERS>, 256, 0);
   if (oe != cudaSuccess || per_sm < 1) per_sm = 2;
   int64_t blocks = ((zero_grads ? n : hi - lo) / 4 + 255) / 256;
@@ -184,8 +188,8 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
   adam_sharded_kernel<W><<<(int)blocks, 256, 0, as_stream(stream)>>>(P, world, rank, params_f32, exp_avg, exp_avg_sq, lo / 4, hi / 4,   \
                                                                     n_sharded / 4, n / 4, zero_grads, n / 4, step_size, beta1, beta2,   \
                                                                     eps, inv_sqrt_bc2, grad_scale)
-  if (world <= 2) RNB_LAUNCH_ADAM_SHARDED(2);
-  else if (world <= 4) RNB_LAUNCH_ADAM_SHARDED(4);
+  if (width == 2) RNB_LAUNCH_ADAM_SHARDED(2);
+  else if (width == 4) RNB_LAUNCH_ADAM_SHARDED(4);
   else RNB_LAUNCH_ADAM_SHARDED(RNB_MAX_PEERS);
 #undef RNB_LAUNCH_ADAM_SHARDED
   return check_launch(what);

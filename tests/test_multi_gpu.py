@@ -109,3 +109,22 @@ def test_two_rank_step_matches_single_process():
     differ2 = ((res2[0][1] - p32_0).abs() > 1e-3).float().mean()
     assert float(differ2) < 0.01
     assert abs(res2[0][2][-1][0] - losses0[-1][0]) < 1e-3 * max(1.0, abs(losses0[-1][0]))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("width", [4, 8])
+def test_wider_peer_kernel_instantiations(width, monkeypatch):
+    """The 4- and 8-peer instantiations of the peer-memory optimizer kernel (used at N = 3..8) run here on two ranks
+    through the RNB_PEER_MIN_WIDTH hook.  Same reduction order as the 2-peer kernel, but two runs never see the same
+    gradient bits (the table scatter is fp32 atomics), so the comparison is the one used against the single process:
+    replicas bit-identical within the run, parameters equal except where the gradient is at rounding level, same loss."""
+    monkeypatch.delenv("RNB_PEER_MIN_WIDTH", raising=False)
+    base = _run(2, True)
+    monkeypatch.setenv("RNB_PEER_MIN_WIDTH", str(width))
+    wide = _run(2, True)
+    assert torch.equal(wide[0][0], wide[1][0]) and torch.equal(wide[0][1], wide[1][1])
+    diff = (base[0][1] - wide[0][1]).abs()
+    print("width", width, "max |dp|", float(diff.max()), "fraction > 1e-3", float((diff > 1e-3).float().mean()))
+    assert float((diff > 1e-3).float().mean()) < 0.01
+    for (a, _), (b, _) in zip(base[0][2], wide[0][2]):
+        assert abs(a - b) < 1e-3 * max(1.0, abs(a))
