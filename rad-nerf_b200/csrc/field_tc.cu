@@ -203,7 +203,10 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
     // warpgroups that took the odd tile of one pass are not the ones that take it in the next (with a fixed start, the
     // first CTAs carried ceil(tiles / warpgroups) in EVERY pass and set the kernel's duration).
     const int64_t tstride = (int64_t)gridDim.x * kWG;
-    int64_t tile0 = (int64_t)blockIdx.x * kWG + wg - tiles_before % tstride;
+    // warpgroup ids interleave the CTAs (wg-major): the tiles of a partial last round then spread over all SMs, a few
+    // warpgroups each, instead of filling some SMs and leaving others empty
+    // (forward 0.140 -> 0.135 ms; the backward kernel, whose tiles are latency- rather than throughput-bound, keeps CTA-major ids)
+    int64_t tile0 = (int64_t)wg * gridDim.x + blockIdx.x - tiles_before % tstride;
     if (tile0 < 0) tile0 += tstride;
     tiles_before += n_tiles;
     float nt = 0.f, nox = 0.f, noy = 0.f, noz = 0.f, ndx = 0.f, ndy = 0.f, ndz = 0.f;
