@@ -28,6 +28,7 @@ sys.path.insert(0, ROOT)
 
 BATCH = 8192
 N_BATCHES = 8          # distinct pre-generated batches cycled through
+TRAFFIC_JSON = "r02_traffic.json"   # ncu --set full DRAM bytes per launch of the current build (scripts/profile_round.sh)
 
 
 def workload(name):
@@ -164,53 +165,91 @@ STAGE_FLOPS = {
 }
 
 
-def run_reference(args):
-    """The reference's math for the same step, in plain PyTorch + the C restatement of its kernels,
-    on the host cores (the reference itself has no CPU implementation of this path)."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
+def arm_config(args, w, world):
+    """The workload description, IDENTICAL in both arms (product and --impl reference)."""
+    return {"workload": args.workload, "K": w["K"], "scale": w["scale"], "batch_rays_per_gpu": BATCH,
+            "step": "forward only (AABB + march + composite)" if w.get("forward_only") else "fwd + loss + bwd + Adam",
+            "params": "tcnn-style random init", "occupancy": "analytic scene, fixed", "parallelism": f"ray-sharded dp{world}",
+            "l2": "GPU arm: flushed between steps (256 MiB write, its time subtracted; the un-flushed loop is reported beside it "
+                  "as ms_per_step_noflush); reference arm: host run"}
+
+
+def cpu_reference(args, steps, warmup):
+    """The reference's math for the same step on the host cores: plain PyTorch + the C restatement of its kernels
+    (the reference itself has no CPU implementation of this path).  FIXED batch of BATCH rays per step -- never sized
+    from a timing -- `warmup` untimed steps, then `steps` timed ones; the value is BATCH / median step time."""
     import torch
     syn, w = workload(args.workload)
     from oracle import render_cpu as R
+    from oracle import vren_cpu as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     os.environ.setdefault("OMP_NUM_THREADS", str(cores))
     K = w["K"]
     bfs = scene_bitfields(syn, w)
-    P = R.FieldParams(w["scale"], K, seed=0).requires_grad_(True)
-    opt = torch.optim.Adam(list(P.p.values()), 1e-2, eps=1e-15)
     esf = syn.exp_step_factor_for_scale(w["scale"])
     C = syn.cascades_for_scale(w["scale"])
     batches = make_batches(syn, w, 0, n_batches=2)
     rng = np.random.RandomState(7)
+    n = BATCH
+    if w.get("forward_only"):
+        # BASELINE config 1 (BASELINE.md 3.1): NGP K = 1 volume-render FORWARD: ray-AABB + marching in the C restatement
+        # (OpenMP over rays; raymarching.cu:184-280), compositing in plain PyTorch CPU ops following volumerendering.cu:23-44,
+        # white background (rendering.py:229-237).  sigma / rgb come from the analytic scene, computed per batch outside
+        # the timed region, so the timed region is sampling + compositing only.
+        scene = syn.make_scene(w["scale"], 1234)
+        pre = []
+        for (o, d, _) in batches:
+            nz = rng.rand(n).astype(np.float32)
+            h = R.hits_for(o, d, w["scale"])
+            _, xyzs, _, _, _, _ = O.raymarching_train(o, d, h, bfs[0], C, w["scale"], esf, nz)
+            pre.append((nz, torch.from_numpy(scene.density(xyzs)), torch.from_numpy(scene.color(xyzs))))
 
-    def step(n):
-        o, d, t = (a[:n] for a in batches[step.i % 2]); step.i += 1
-        noises = [rng.rand(n).astype(np.float32) for _ in range(K)]
-        res = R.ml_render_train(P, o, d, bfs, noises, C, esf)
-        loss, _ = R.nerf_loss(res, torch.from_numpy(t), 1e-3, 1e-2 if K > 1 else 0, 5e-3 if K > 1 else 0)
-        opt.zero_grad(); loss.backward(); opt.step()
-        return float(loss)
-    step.i = 0
-    t0 = time.time(); step(128); probe = time.time() - t0
-    budget = 90.0   # seconds for warmup + timed steps
-    n = int(max(64, min(BATCH, 128 * budget / max(probe, 1e-3) / (args.steps + args.warmup))))
-    n = n // 64 * 64
-    for _ in range(args.warmup):
-        step(n)
-    t0 = time.time()
-    for _ in range(args.steps):
-        step(n)
-    dt = time.time() - t0
-    val = n * args.steps / dt
-    sample = f"{n} of {BATCH} rays per step (same scene/cameras/K), fwd+loss+bwd+Adam"
+        def step(i):
+            o, d, _ = batches[i % 2]
+            nz, sig, col = pre[i % 2]
+            h = R.hits_for(o, d, w["scale"])
+            rays_a, xyzs, dirs, deltas, ts, _ = O.raymarching_train(o, d, h, bfs[0], C, w["scale"], esf, nz)
+            with torch.no_grad():
+                opacity, depth, rgb, ws, tot = R.composite_train(sig, col, torch.from_numpy(deltas), torch.from_numpy(ts), rays_a, 1e-4)
+                rgb = rgb + (1 - opacity)[:, None]
+            return float(rgb.sum())
+        what = "forward only: C marcher (OpenMP) + plain-PyTorch composite"
+    else:
+        P = R.FieldParams(w["scale"], K, seed=0).requires_grad_(True)
+        opt = torch.optim.Adam(list(P.p.values()), 1e-2, eps=1e-15)
+
+        def step(i):
+            o, d, t = batches[i % 2]
+            noises = [rng.rand(n).astype(np.float32) for _ in range(K)]
+            res = R.ml_render_train(P, o, d, bfs, noises, C, esf)
+            loss, _ = R.nerf_loss(res, torch.from_numpy(t), 1e-3, 1e-2 if K > 1 else 0, 5e-3 if K > 1 else 0)
+            opt.zero_grad(); loss.backward(); opt.step()
+            return float(loss.detach())
+        what = "fwd+loss+bwd+Adam"
+    for i in range(warmup):
+        step(i)
+    times = []
+    for i in range(steps):
+        t0 = time.perf_counter(); step(warmup + i); times.append(time.perf_counter() - t0)
+    med = float(np.median(times))
+    return {"value": n / med, "unit": "rays/s", "cores": cores, "kind": "port",
+            "sample": f"{n} of {BATCH} rays per step (fixed; same scene/cameras/K), {what}; {warmup} warm-up + median of {steps} timed steps",
+            "ms_per_step": 1e3 * med, "ms_min": 1e3 * min(times), "ms_max": 1e3 * max(times)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    syn, w = workload(args.workload)
+    cb = cpu_reference(args, max(args.steps, 1), args.warmup)
+    val = cb["value"]
     line = {"impl": "reference", "metric": "train_rays_per_s", "value": val, "unit": "rays/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp16 rounding points)", "data": "synthetic",
-            "config": {"workload": args.workload, "K": K, "scale": w["scale"], "batch_rays_per_gpu": BATCH,
-                       "params": "tcnn-style random init", "occupancy": "analytic scene, fixed"},
-            "cpu_baseline": {"value": val, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": arm_config(args, w, args.gpus),
+            "cpu_baseline": cb,
             "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -347,6 +386,12 @@ def run_product(args):
     launches = _lib.launch_count - n0
     clk = clocks.stop()
     ms_step = ms / args.steps - flush_ms
+    # the same loop without the L2 flush (nothing subtracted): parameters and inputs of the previous step stay in L2
+    def noflush_step(s):
+        nxt = dev[(s + 1) % len(dev)]
+        tr.step(*dev[s % len(dev)], next_rays=nxt[:2] if ahead else None)
+    noflush_step(0)
+    ms_noflush = timed(lambda s: noflush_step(s + 1), args.steps) / args.steps
     for s in range(args.warmup):         # untimed: feeder slots, copy / read-back streams and pinned buffers come up here
         e2e_step(s)
     e2e_ms = timed(lambda s: e2e_step(s + args.warmup), args.steps) / args.steps - flush_ms
@@ -361,6 +406,21 @@ def run_product(args):
         lib.rnb_engine_profile_read(arr_ms, arr_n, 16)
         lib.rnb_engine_profile(0)
         stage_ms = {STAGES[i]: (arr_ms[i] / max(arr_n[i], 1), arr_n[i]) for i in range(len(STAGES)) if arr_n[i]}
+    # multi-rank correctness the driver can see: every rank must hold bit-identical fp16 parameters after the timed steps
+    # (one writer per shard in the peer-memory optimizer) and must have seen the same global gate importance
+    replica = None
+    if world > 1 and tr.engine is not None:
+        p16 = tr.engine.flat16.view(torch.int16).to(torch.int64)
+        idx = torch.arange(1, p16.numel() + 1, device=p16.device, dtype=torch.int64)
+        chk = torch.stack([p16.sum(), (p16 * (idx % 65521)).sum(),
+                           tr.engine.importance.double().sum().mul(1e6).round().to(torch.int64)])
+        allc = [torch.zeros_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        same = all(bool(torch.equal(allc[0], c)) for c in allc)
+        replica = {"status": "ok" if same else "MISMATCH", "ranks": world,
+                   "flat16_checksum": [int(x) for x in allc[0][:2].tolist()],
+                   "what": "fp16 parameter vector (two 64-bit checksums) and global gate importance equal on every rank after the timed steps"}
+        assert same, f"replicas diverged: {[c.tolist() for c in allc]}"
     rays_total = BATCH * world
     value = rays_total / (ms_step * 1e-3)
     e2e_val = rays_total / (e2e_ms * 1e-3)
@@ -372,12 +432,11 @@ def run_product(args):
     line = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16 (fp32 accumulate; fp32 march/composite)", "data": "synthetic",
-            "config": {"workload": args.workload, "K": K, "scale": w["scale"], "batch_rays_per_gpu": BATCH,
-                       "params": "tcnn-style random init",
-                       "occupancy": "analytic scene, fixed; grid update every 16 steps runs on shadow grids",
-                       "l2": "flushed between steps (256 MiB write, its time subtracted)",
-                       "march_ahead": bool(ahead), "parallelism": f"ray-sharded dp{world}",
-                       "path": "fused engine (rnb_engine_*)" if tr.engine is not None else "python operator surface"},
+            "config": arm_config(args, w, world),
+            "run": {"occupancy_update": "every 16 steps, on shadow grids (the marched occupancy stays the analytic scene's)",
+                    "march_ahead": bool(ahead),
+                    "path": "fused engine (rnb_engine_*)" if tr.engine is not None else "python operator surface"},
+            "ms_per_step_noflush": ms_noflush, "value_noflush": rays_total / (ms_noflush * 1e-3),
             "clocks": clk,
             "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * BATCH * 12, "d2h_bytes_per_step": 32,
                     "ms_per_step": e2e_ms},
@@ -385,8 +444,8 @@ def run_product(args):
     if tr.engine is not None:
         counts, overflow = tr.engine.sample_stats()
         N = float(sum(counts)); KR = float(K * BATCH); Pn = float(tr.engine.n_params)
-        line["config"]["samples_per_ray"] = N / KR
-        line["config"]["sample_overflow"] = overflow
+        line["run"]["samples_per_ray"] = N / KR
+        line["run"]["sample_overflow"] = overflow
         top = max(stage_ms, key=lambda k: stage_ms[k][0] * stage_ms[k][1])
         t_ms = stage_ms[top][0]
         fb = STAGE_BYTES.get(top, lambda *a: 0)(N, KR, Pn) / (t_ms * 1e-3) / 1e9
@@ -398,7 +457,7 @@ def run_product(args):
         # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/, same workload and batch)
         traffic = None
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["kernels"]
+            tj = json.load(open(os.path.join(ROOT, "profiles", TRAFFIC_JSON)))["kernels"]
             kname = {"field_bwd": "field_bwd_tc_kernel", "field_fwd": "field_fwd_tc_kernel<1>", "march": "eng_march_kernel<1>",
                      "adam": "eng_adam_kernel"}.get(top)
             if kname in tj and args.workload == "radnerf_tat_k2" and tr.engine is not None:
@@ -411,22 +470,130 @@ def run_product(args):
                      "stage_ms_per_launch": {k: round(v[0], 4) for k, v in stage_ms.items()},
                      "stages_share_of_step": sum(v[0] * v[1] for v in stage_ms.values()) / args.steps / ms_step})
         line["roofline"] = roof
+    if replica is not None:
+        line["replica_check"] = replica["status"]
+        line["replica"] = replica
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
+        line["gpu_anchor"] = gpu_anchor()
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def cpu_baseline(args):
-    """Oracle (CPU port of the reference's math) on a bounded sample of the same workload."""
+def run_product_fwd_only(args):
+    """BASELINE config 1 on the GPU: the volume-render FORWARD (ray-AABB, training march, compositing, white background) of
+    an Instant-NGP K = 1 model through this library's `vren` operator surface, sigma / rgb supplied by the analytic scene
+    (computed per batch outside the timed region): the timed region is sampling + compositing, as in the CPU arm."""
+    import torch
+    torch.cuda.set_device(0)
+    syn, w = workload(args.workload)
+    from radnerf_b200 import _lib, vren
+    _lib.lib()
+    sc = syn.make_scene(w["scale"], 1234)
+    bf = torch.from_numpy(scene_bitfields(syn, w)[0]).cuda()
+    host = [tuple(torch.from_numpy(a).pin_memory() for a in b) for b in make_batches(syn, w, 0)]
+    center = torch.zeros(1, 3, device="cuda"); half = torch.full((1, 3), float(w["scale"]), device="cuda")
+    rng = np.random.RandomState(7)
+    noise = [torch.from_numpy(rng.rand(BATCH).astype(np.float32)).cuda() for _ in host]
+    flush = torch.empty(256 * 1024 * 1024 // 4, device="cuda")
+
+    def fwd(o, d, nz, sig=None, col=None):
+        _, hits_t, _ = vren.ray_aabb_intersect(o, d, center, half, 1)
+        h = hits_t[:, 0].contiguous()
+        h[(h[:, 0] >= 0) & (h[:, 0] < syn.NEAR_DISTANCE), 0] = syn.NEAR_DISTANCE
+        rays_a, xyzs, dirs, deltas, ts, counter = vren.raymarching_train(o, d, h, bf, 1, w["scale"], 0.0, nz, 128, 1024)
+        if sig is None:
+            return xyzs
+        _, opacity, depth, rgb, ws = vren.composite_train_fw(sig, col, deltas, ts, rays_a, 1e-4)
+        return rgb + (1 - opacity)[:, None]
+
+    pre = []
+    for (o, d, _), nz in zip(host, noise):
+        x = fwd(o.cuda(), d.cuda(), nz).cpu().numpy()
+        pre.append((torch.from_numpy(sc.density(x)).cuda(), torch.from_numpy(sc.color(x)).cuda()))
+    dev = [tuple(a.cuda() for a in b) for b in host]
+    n0 = None
+
+    def timed(fn, steps):
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s in range(steps):
+            fn(s)
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    def dev_step(s):
+        flush.add_(1.0)
+        k = s % len(dev)
+        fwd(dev[k][0], dev[k][1], noise[k], *pre[k])
+
+    out_pin = torch.zeros(BATCH, 3).pin_memory()
+
+    def e2e_step(s):
+        flush.add_(1.0)
+        k = s % len(host)
+        o, d = host[k][0].cuda(non_blocking=True), host[k][1].cuda(non_blocking=True)
+        out_pin.copy_(fwd(o, d, noise[k], *pre[k]), non_blocking=True)
+
+    for s in range(args.warmup):
+        dev_step(s); e2e_step(s)
+    flush_ms = timed(lambda s: flush.add_(1.0), args.steps)
+    clocks = ClockSampler(0); clocks.start()
+    n0 = _lib.launch_count
+    ms = timed(dev_step, args.steps) - flush_ms
+    launches = _lib.launch_count - n0
+    clk = clocks.stop()
+    e2e_ms = timed(e2e_step, args.steps) - flush_ms
+    line = {"metric": "train_rays_per_s", "value": BATCH / (ms * 1e-3), "unit": "rays/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": arm_config(args, w, 1),
+            "run": {"path": "vren operator surface (rnb_ray_aabb_intersect, rnb_march_train_*, rnb_composite_train_fw)"},
+            "clocks": clk, "gpu_launches": launches,
+            "e2e": {"value": BATCH / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": 2 * BATCH * 12,
+                    "d2h_bytes_per_step": BATCH * 12, "ms_per_step": e2e_ms}}
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args)
+    print(json.dumps(line))
+
+
+def _json_lines(cmd, timeout):
     import subprocess as sp
-    out = sp.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "2", "--warmup", "1",
-                  "--workload", args.workload], capture_output=True, text=True, timeout=600)
-    for ln in out.stdout.splitlines()[::-1]:
+    out = sp.run(cmd, capture_output=True, text=True, timeout=timeout)
+    rows = []
+    for ln in out.stdout.splitlines():
         if ln.startswith("{"):
-            return json.loads(ln)["cpu_baseline"]
-    return {"value": None, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: " + out.stderr[-200:]}
+            try:
+                rows.append(json.loads(ln))
+            except ValueError:
+                pass
+    return rows, out.stderr[-300:]
+
+
+def cpu_baseline(args):
+    """The reference arm (oracle port of the reference's math, all host cores) on the same fixed 8192-ray batch:
+    3 warm-up steps + median of 5.  Runs in a subprocess so that this (product) process never loads oracle/."""
+    rows, err = _json_lines([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "5", "--warmup", "3",
+                             "--workload", args.workload], 900)
+    if rows:
+        return rows[-1]["cpu_baseline"]
+    return {"value": None, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: " + err}
+
+
+def gpu_anchor():
+    """The reference's OWN kernels (oracle/_ref/vren_ref, compiled unmodified for sm_100a) next to this library's operators
+    on the training shape (tests/anchor_vren_ref.py; subprocess: the product process never loads the reference)."""
+    import glob
+    if not glob.glob(os.path.join(ROOT, "oracle", "_ref", "vren_ref*.so")):
+        return {"unavailable": "oracle/_ref/vren_ref*.so not built (needs /root/reference at build time)"}
+    try:
+        rows, err = _json_lines([sys.executable, os.path.join(ROOT, "tests", "anchor_vren_ref.py"), "--training-shape-only"], 600)
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": str(e)[:200]}
+    if not rows:
+        return {"unavailable": "anchor failed: " + err}
+    return {r["op"]: {"ref_ms": r["reference_kernels_ms"], "ours_ms": r["ours_ms"]} for r in rows}
 
 
 def main():
@@ -443,6 +610,8 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args)
+    elif workload(args.workload)[1].get("forward_only"):
+        run_product_fwd_only(args)
     else:
         run_product(args)
 

@@ -264,6 +264,12 @@ int rnb_field_bwd(const rnb_field_params* P, const rnb_samples* S, const rnb_fie
                   const void* rgb4_f16, const float* dL_dsigmas, const float* dL_drgbs,
                   float loss_scale, float* grad_table, float* const* grad_geo, float* const* grad_rgb,
                   rnb_stream_t stream);
+/* The same; additionally ORs RNB_FLAG_NONFINITE into *flags (may be NULL) when a gradient seed saturates fp16 at this
+ * loss_scale or an inf / nan reaches the gradient of the encoding (hence of the table). */
+int rnb_field_bwd_guarded(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved,
+                          const void* rgb4_f16, const float* dL_dsigmas, const float* dL_drgbs,
+                          float loss_scale, float* grad_table, float* const* grad_geo, float* const* grad_rgb,
+                          int32_t* flags, rnb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * (fused step) One Rad-NeRF training step without host synchronisation.  Replaces the body of
@@ -317,7 +323,22 @@ typedef struct {
   int64_t march_slot_bytes;
   int64_t coarse;                /* u64 (K,4096): dilated 64^3-block occupancy (bit x of word y + 64 z), part of the march slot; used
                                   * for the marcher's empty-space test when cascades == 1 and grid_size == 128     */
+  int64_t status;                /* i32 (8) step guard (GradScaler equivalent, see rnb_engine_adam_guarded): [0] optimizer steps skipped
+                                  * for a non-finite / saturated gradient, [1] steps skipped because the samples exceeded
+                                  * sample_capacity, [2] largest (128-aligned) sample count any step needed, [3] optimizer steps
+                                  * applied, [4] internal ticket.  The caller zeroes it once; the library only counts up. */
 } rnb_engine_layout;
+
+/* Step guard.  The reference trains with Lightning precision=16 (train_ml.py:304): a dynamic GradScaler that skips the
+ * optimizer step when a gradient is inf / nan and adapts the loss scale.  Here the gradient buffer carries
+ * RNB_GRAD_TAIL extra floats behind the n_params gradients; word [n_params] is this step's FLAG word (i32 bit mask):
+ * producers (blend kernel, field backward, rnb_engine_grad_check) OR bits into it, the Adam kernels read it -- in the
+ * sharded optimizer every rank reads every peer's word, so all ranks take the same decision -- and, when it is set,
+ * clear the gradients WITHOUT touching parameters or moments.  rnb_engine_fwd_bwd[_ex] clears the word at the start of
+ * a step with_backward.  The host adapts cfg->loss_scale from the status counters (no synchronisation needed). */
+#define RNB_GRAD_TAIL 64
+#define RNB_FLAG_NONFINITE 1      /* a gradient seed saturated fp16, or an inf / nan reached a parameter gradient */
+#define RNB_FLAG_CAPACITY 2       /* the step's samples did not fit sample_capacity (the tail was dropped)        */
 
 int rnb_engine_layout_of(const rnb_engine_config* cfg, rnb_engine_layout* out);
 
@@ -329,7 +350,8 @@ int rnb_engine_gate(const rnb_engine_config* cfg, void* workspace, const void* p
  * the GLOBAL importance (all-reduced over ranks when data parallel; the workspace's own buffer otherwise).
  * n_rays_global: rays of the whole (multi-rank) batch, the denominator of the loss means.
  * bitfields: HOST array of K device pointers; noise (K,n_rays) f32 device in [0,1); bg (K,3) f32 HOST
- * (background colour per pass, Q17).  Gradients are ACCUMULATED into grads_f32 (flat, fp32). */
+ * (background colour per pass, Q17).  Gradients are ACCUMULATED into grads_f32 (flat, fp32; n_params + RNB_GRAD_TAIL floats:
+ * the flag word of the step guard sits at index n_params and is cleared at the start of a step with_backward). */
 int rnb_engine_fwd_bwd(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* grads_f32,
                        const float* rays_o, const float* rays_d, const float* target_rgb, const float* noise,
                        const uint8_t* const* bitfields, const float* bg_host, int64_t n_rays_global,
@@ -360,6 +382,16 @@ int rnb_engine_march(const rnb_engine_config* cfg, void* workspace, const float*
 int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq,
                     int64_t n, float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                     rnb_stream_t stream);
+/* The same behind the step guard: `flags` = the gradient buffer's flag word (grads_f32 + n as i32), `status` = the
+ * workspace's status block.  Flag set: gradients are cleared, parameters / moments / fp16 copy stay, status[0] or [1]
+ * counts the skip.  Flag clear: the update is applied with the bias corrections of step status[3] + 1 (the count of
+ * APPLIED steps lives on the device, like GradScaler's skipped steps do not advance the optimizer), status[3]++. */
+int rnb_engine_adam_guarded(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq,
+                            int64_t n, float lr, float beta1, float beta2, float eps, float grad_scale,
+                            const int32_t* flags, int32_t* status, rnb_stream_t stream);
+/* ORs RNB_FLAG_NONFINITE into *flags when grads_f32[lo, hi) holds an inf or nan (used on the dense-network block: the
+ * table gradient is checked where it is produced, in the field backward kernel). */
+int rnb_engine_grad_check(const float* grads_f32, int64_t lo, int64_t hi, int32_t* flags, rnb_stream_t stream);
 
 /* Ray_Gate.forward (networks.py:1087-1093): logits = MLP(cat(rays_o, rays_d) padded with ones to 16), softmax over
  * the K logits in fp32, importance[k] = sum over rays.  gate_hidden_f16 ((4,n_rays,64), saved for the backward
@@ -444,6 +476,13 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
                             float* params_f32, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded,
                             float* zero_grads, float lr, float beta1, float beta2, float eps, int64_t step,
                             float grad_scale, rnb_stream_t stream);
+/* The same behind the step guard (see RNB_GRAD_TAIL): every peer gradient buffer carries its flag word at float index n;
+ * the kernel ORs all of them (peer loads), so every rank skips or applies the same step.  status: this rank's status
+ * block (step count of applied steps as in rnb_engine_adam_guarded). */
+int rnb_engine_adam_sharded_guarded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers,
+                                    float* params_f32, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded,
+                                    float* zero_grads, float lr, float beta1, float beta2, float eps, float grad_scale,
+                                    int32_t* status, rnb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * (callers of the path) Training-batch assembly on the device: replaces BaseDataset.__getitem__'s pixel sampling
@@ -469,11 +508,6 @@ int rnb_engine_profile_span_end(int handle, rnb_stream_t stream);
 /* The same records as a timeline (issue order): stage index, start and end in ms relative to the first record; the
  * events of the step's side streams share the device clock, so overlap and gaps between stages are visible. */
 int rnb_engine_profile_timeline(int32_t* stage, double* start_ms, double* end_ms, int n_max, int32_t* n_out);
-
-/* Selects the implementation behind rnb_field_fwd / rnb_field_bwd: 1 = tcgen05 + TMEM kernels
- * (csrc/field_tc.cu, default where available), 0 = mma.sync register-chained kernels (csrc/field.cu).
- * Both compute the same operator; the switch exists for A/B measurement and parity tests. */
-int rnb_set_field_impl(int fwd_tcgen05, int bwd_tcgen05);   /* both or neither: the saved layouts differ */
 
 /* Diagnostics: self-test of the tcgen05 building blocks (csrc/tc05.cuh) on one CTA.
  * X (128,64), W (64,64), Y (128,32) f16 row-major -> out1 (128,64) = X W^T, out2 (128,32) = raw TMEM

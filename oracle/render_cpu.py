@@ -188,3 +188,72 @@ def render_test(P: FieldParams, rays_o, rays_d, bitfield, i, cascades, exp_step_
     bg = np.ones(3, np.float32) if exp_step_factor == 0 else np.zeros(3, np.float32)
     rgb = rgb + bg * (1 - opacity)[:, None]
     return {"opacity": opacity, "depth": depth, "rgb": rgb, "total_samples": total}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Occupancy-grid update: MNGP.update_density_grid (networks.py:374-409) with its helpers get_all_cells (:330-342)
+# and sample_uniform_and_occupied_cells (:344-372), for ONE sub-NeRF i.  Every random draw of the reference
+# (`torch.randint` coords1 :359, `torch.randint(len(indices2))` :365, `torch.rand_like` jitter :391) is an INPUT
+# here so that the CUDA path can be fed the same numbers:
+#   coords1 (C, M, 3) int32 in [0,G)                              -- the uniform cells (M = G^3 // 4, :381)
+#   pick_u  (C, M)    f32  in [0,1)   rand_idx = min(int(u*n), n-1) -- stands for randint(n) over the occupied list
+#   noise   (C, M_c, 3) f32 in [0,1)                               -- the jitter, M_c = G^3 (warm-up) or 2M
+# Returns a dict:
+#   cells[c]  int64 indices evaluated in cascade c, in the reference's order (uniform cells, then occupied picks)
+#   sigma[c]  density at each of them
+#   tmp_last  density_grid_tmp as numpy's last-write-wins scatter leaves it (ONE legal outcome of the reference's
+#             index_put with duplicate indices, whose winner CUDA leaves undefined), with tmp_lo / tmp_hi the
+#             smallest / largest candidate per cell (every legal outcome lies between them)
+#   grid, grid_lo, grid_hi  where(grid<0, grid, max(grid*decay, tmp)) for the three tmp variants (:397-400)
+#   mean      grid[grid>0].mean() (:402);  thr = min(mean, density_threshold);  bitfield = packbits(grid, thr) (:403-404)
+def update_density_grid(P: FieldParams, i, density_grid, density_threshold, warmup, noise, coords1=None, pick_u=None,
+                        decay=0.95, grid_size=128):
+    G = grid_size
+    G3 = G ** 3
+    grid = np.ascontiguousarray(density_grid, dtype=np.float32)
+    C = grid.shape[0]
+    cells, coords = [], []
+    if warmup:                                                     # get_all_cells: every cell, morton order = index order
+        all_idx = np.arange(G3, dtype=np.int32)
+        all_coords = O.morton3D_invert(all_idx)
+        for c in range(C):
+            cells.append(all_idx.astype(np.int64)); coords.append(all_coords)
+    else:
+        for c in range(C):
+            c1 = np.ascontiguousarray(coords1[c], dtype=np.int32)
+            idx1 = O.morton3D(c1).astype(np.int64)
+            occ = np.nonzero(grid[c] > np.float32(density_threshold))[0]
+            if len(occ) > 0:
+                n = len(occ)
+                ridx = np.minimum((np.asarray(pick_u[c], np.float32) * np.float32(n)).astype(np.int64), n - 1)
+                idx2 = occ[ridx]
+                c2 = O.morton3D_invert(idx2.astype(np.int32))
+                cells.append(np.concatenate([idx1, idx2])); coords.append(np.concatenate([c1, c2]))
+            else:
+                cells.append(idx1); coords.append(c1)
+    tmp_last = np.zeros_like(grid); tmp_lo = np.full_like(grid, np.inf); tmp_hi = np.zeros_like(grid)
+    touched = np.zeros(grid.shape, bool)
+    sigmas = []
+    for c in range(C):
+        s = min(2 ** (c - 1), P.scale)
+        half = s / G
+        cc = torch.from_numpy(coords[c].astype(np.float32))
+        nz = torch.from_numpy(np.ascontiguousarray(noise[c][:len(cells[c])], dtype=np.float32))
+        xyzs_w = (cc / (G - 1) * 2 - 1) * (s - half)
+        xyzs_w = xyzs_w + (nz * 2 - 1) * half
+        with torch.no_grad():
+            sig = density(P, i, xyzs_w).numpy().astype(np.float32)
+        sigmas.append(sig)
+        tmp_last[c][cells[c]] = sig
+        np.minimum.at(tmp_lo[c], cells[c], sig); np.maximum.at(tmp_hi[c], cells[c], sig)
+        touched[c][cells[c]] = True
+    tmp_lo[~touched] = 0.0
+
+    def ema(t):
+        return np.where(grid < 0, grid, np.maximum(grid * np.float32(decay), t)).astype(np.float32)
+    new = ema(tmp_last)
+    mean = float(new[new > 0].astype(np.float64).mean()) if (new > 0).any() else 0.0
+    thr = min(mean, float(density_threshold))
+    return {"cells": cells, "sigma": sigmas, "touched": touched, "tmp_last": tmp_last, "tmp_lo": tmp_lo, "tmp_hi": tmp_hi,
+            "grid": new, "grid_lo": ema(tmp_lo), "grid_hi": ema(tmp_hi), "mean": mean, "thr": thr,
+            "bitfield": O.packbits(new, thr)}

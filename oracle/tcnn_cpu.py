@@ -38,18 +38,46 @@ def h16(x: torch.Tensor) -> torch.Tensor:
     return x + (x.half().float() - x).detach()
 
 
+_LIBM = None
+
+
+def _libm():
+    import ctypes
+    global _LIBM
+    if _LIBM is None:
+        _LIBM = ctypes.CDLL("libm.so.6")
+        for f in ("exp2f", "log2f", "ceilf"):
+            getattr(_LIBM, f).restype = ctypes.c_float
+            getattr(_LIBM, f).argtypes = [ctypes.c_float]
+    return _LIBM
+
+
+def level_scale_res(level, b, base_res, rule="tcnn_fp32"):
+    """tinycudann grid.h: grid_scale() = exp2f(level * log2_per_level_scale) * base_resolution - 1.0f and
+    grid_resolution() = (uint32_t)ceilf(scale) + 1, evaluated on the host in fp32 by the encoding's constructor with
+    log2_per_level_scale = std::log2(float per_level_scale).  `rule="fp64_snap"` is the round-1 rule (fp64, 6-decimal
+    snap), kept for comparison: it differs where the real-valued scale is an integer (scene scale 0.5: levels 5/10/15)."""
+    import ctypes
+    if rule == "fp64_snap":
+        s = round(float(np.exp2(level * np.log2(b)) * base_res - 1.0), 6)
+        return s, int(np.ceil(s)) + 1
+    m = _libm()
+    f = np.float32
+    log2b = f(m.log2f(ctypes.c_float(f(b))))
+    e = f(f(level) * log2b)
+    s = f(f(f(m.exp2f(ctypes.c_float(e))) * f(base_res)) - f(1.0))
+    return float(s), int(m.ceilf(ctypes.c_float(s))) + 1
+
+
 class GridMeta:
-    def __init__(self, n_levels=16, n_features=2, log2_T=19, base_res=16, per_level_scale=1.3195079565048218):
+    def __init__(self, n_levels=16, n_features=2, log2_T=19, base_res=16, per_level_scale=1.3195079565048218, rule=None):
+        import os
+        rule = rule or os.environ.get("RNB_GRID_LEVEL_RULE", "tcnn_fp32")
         self.L, self.F, self.log2_T, self.N_min = n_levels, n_features, log2_T, base_res
         self.b = float(per_level_scale)
-        log2b = np.log2(self.b)
         self.scales, self.res, self.offsets, self.sizes = [], [], [0], []
         for l in range(n_levels):
-            # tcnn evaluates exp2f(l*log2(b))*N_min - 1 in fp32; whether a level whose scale is an
-            # exact integer (e.g. 63 at level 5 for b = 64^(1/15)) lands on res or res+1 depends on
-            # libm rounding.  We fix the rule: evaluate in fp64, snap fp noise (6 decimals), then ceil.
-            s = round(float(np.exp2(l * log2b) * base_res - 1.0), 6)
-            r = int(np.ceil(s)) + 1
+            s, r = level_scale_res(l, self.b, base_res, rule)
             n = min(r ** 3, 2 ** 31 - 1)
             n = (n + 7) // 8 * 8
             n = min(n, 1 << log2_T)

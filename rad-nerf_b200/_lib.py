@@ -74,7 +74,7 @@ def stream_arg(device=None):
 
 
 # kernels launched per C-ABI call (for bench.py's `gpu_launches` claim)
-KERNELS_PER_CALL = {"rnb_raymarching_train_count": 2, "rnb_engine_gate": 3, "rnb_engine_fwd_bwd": 9, "rnb_engine_fwd_bwd_ex": 8, "rnb_engine_gate_bwd": 1, "rnb_engine_adam": 1,
+KERNELS_PER_CALL = {"rnb_raymarching_train_count": 2, "rnb_engine_gate": 3, "rnb_engine_fwd_bwd": 9, "rnb_engine_fwd_bwd_ex": 8, "rnb_engine_gate_bwd": 1, "rnb_engine_adam": 1, "rnb_engine_adam_guarded": 1, "rnb_engine_grad_check": 1,
                     "rnb_engine_layout_of": 0, "rnb_grid_update_layout_of": 0, "rnb_render_layout_of": 0,
                     "rnb_grid_update": 5, "rnb_engine_march": 3}
 launch_count = 0

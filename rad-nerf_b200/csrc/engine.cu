@@ -14,6 +14,7 @@
 #include "composite.cuh"
 #include "march_warp.cuh"
 #include "coarse.cuh"
+#include "adam.cuh"
 
 namespace rnb {
 
@@ -238,6 +239,8 @@ struct BlendArgs {
   float* d_opacity; float* d_depth; float* d_rgb; __half* dlogits;
   float* loss;
   int with_backward;
+  // step guard (RNB_GRAD_TAIL): the marcher's overflow flag and aligned sample total, the step's flag word, the status block
+  const int32_t* seg; int32_t* flags; int32_t* status;
 };
 
 __global__ void __launch_bounds__(256) eng_blend_loss_kernel(BlendArgs A) {
@@ -245,6 +248,12 @@ __global__ void __launch_bounds__(256) eng_blend_loss_kernel(BlendArgs A) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int K = A.K, R = A.n_rays;
+  if (A.flags != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    // samples beyond sample_capacity were dropped by every kernel of this step: the optimizer must not apply it
+    if (A.seg[2 * K + 1]) atomicOr(A.flags, RNB_FLAG_CAPACITY);
+    atomicMax(A.status + 2, A.seg[K]);
+  }
+  bool saturated = false;
   // CV^2 of the (global) importance and its derivative (losses.py:69-71; unbiased variance)
   float cv = 0.f, dcv[RNB_MAX_K];
 #pragma unroll
@@ -323,8 +332,9 @@ __global__ void __launch_bounds__(256) eng_blend_loss_kernel(BlendArgs A) {
       __half2 out[8];
 #pragma unroll
       for (int k = 0; k < 16; k += 2) {
-        const float v0 = k < K ? fminf(fmaxf(g[k] * (dg[k] - gdot) * A.gs, -65504.f), 65504.f) : 0.f;
-        const float v1 = k + 1 < K ? fminf(fmaxf(g[k + 1] * (dg[k + 1] - gdot) * A.gs, -65504.f), 65504.f) : 0.f;
+        const float u0 = k < K ? g[k] * (dg[k] - gdot) * A.gs : 0.f, u1 = k + 1 < K ? g[k + 1] * (dg[k + 1] - gdot) * A.gs : 0.f;
+        saturated |= !(fabsf(u0) <= 65504.f) || !(fabsf(u1) <= 65504.f);      // also true for nan
+        const float v0 = fminf(fmaxf(u0, -65504.f), 65504.f), v1 = fminf(fmaxf(u1, -65504.f), 65504.f);
         out[k >> 1] = __floats2half2_rn(v0, v1);
       }
       uint4* dst = reinterpret_cast<uint4*>(A.dlogits + (int64_t)r * 16);
@@ -332,6 +342,7 @@ __global__ void __launch_bounds__(256) eng_blend_loss_kernel(BlendArgs A) {
       dst[1] = *reinterpret_cast<const uint4*>(&out[4]);
     }
   }
+  if (A.flags != nullptr && __any_sync(kFullMask, saturated) && lane == 0) atomicOr(A.flags, RNB_FLAG_NONFINITE);
   l_rgb = warp_sum(l_rgb); l_op = warp_sum(l_op); l_dm = warp_sum(l_dm);
   if (lane == 0) { red[warp][0] = l_rgb; red[warp][1] = l_op; red[warp][2] = l_dm; }
   __syncthreads();
@@ -347,10 +358,19 @@ __global__ void __launch_bounds__(256) eng_blend_loss_kernel(BlendArgs A) {
 
 // ---- Adam (torch.optim.Adam, amsgrad = False, weight_decay = 0; train_ml.py:143 uses FusedAdam(eps=1e-15)) ----
 __global__ void __launch_bounds__(256) eng_adam_kernel(float* __restrict__ p, __half* __restrict__ p16, float* __restrict__ g,
-                                                       float* __restrict__ m, float* __restrict__ v, int64_t n, float step_size,
-                                                       float beta1, float beta2, float eps, float inv_sqrt_bc2, float grad_scale) {
+                                                       float* __restrict__ m, float* __restrict__ v, int64_t n, float lr, int64_t host_step,
+                                                       float beta1, float beta2, float eps, float grad_scale,
+                                                       const int32_t* __restrict__ flags, int32_t* __restrict__ status) {
+  __shared__ AdamStep sh;
+  adam_prologue(&sh, flags != nullptr ? *(volatile const int32_t*)flags : 0, status, host_step, lr, beta1, beta2);
+  const float step_size = sh.step_size, inv_sqrt_bc2 = sh.inv_sqrt_bc2;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t n4 = n >> 2;
+  if (sh.skip) {      // a non-finite gradient or dropped samples: clear the gradients, leave parameters and moments alone
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) g[i] = 0.f;
+    return;
+  }
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pp = reinterpret_cast<float4*>(p)[i], gg = reinterpret_cast<float4*>(g)[i];
     float4 mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
@@ -373,6 +393,14 @@ __global__ void __launch_bounds__(256) eng_adam_kernel(float* __restrict__ p, __
     const float pi = p[i] - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
     p[i] = pi; m[i] = mi; v[i] = vi; g[i] = 0.f; p16[i] = __float2half_rn(pi);
   }
+}
+
+// inf / nan anywhere in grads[lo, hi) -> flag (the dense networks' block: a few ten thousand values)
+__global__ void __launch_bounds__(256) eng_grad_check_kernel(const float* __restrict__ g, int64_t lo, int64_t hi, int32_t* __restrict__ flags) {
+  bool bad = false;
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x)
+    bad |= !(fabsf(g[i]) <= 3.0e38f);
+  if (__any_sync(kFullMask, bad) && (threadIdx.x & 31) == 0) atomicOr(flags, RNB_FLAG_NONFINITE);
 }
 
 }  // namespace rnb
@@ -439,6 +467,7 @@ int rnb_engine_layout_of(const rnb_engine_config* c, rnb_engine_layout* L) {
   L->d_pass_opacity = w.take(K * R * 4); L->d_pass_depth = w.take(K * R * 4); L->d_pass_rgb = w.take(K * R * 3 * 4);
   L->rgb = w.take(R * 3 * 4); L->opacity = w.take(R * 4); L->depth = w.take(R * K * 4);
   L->loss = w.take(8 * 4);
+  L->status = w.take(8 * 4);
   L->march_slot_bytes = L->enc - L->t_scratch;     // [t_scratch, counts, starts, seg, ray_id, ts, deltas] are contiguous
   L->march_slot1 = w.take(L->march_slot_bytes);
   L->total_bytes = w.off;
@@ -552,6 +581,10 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   int32_t* seg = (int32_t*)(ws + slot_off + L.seg);
   int32_t* ray_id = (int32_t*)(ws + slot_off + L.ray_id); float* ts = (float*)(ws + slot_off + L.ts); float* deltas = (float*)(ws + slot_off + L.deltas);
   RNB_CUDA(cudaMemsetAsync(ws + L.loss, 0, 8 * 4, st), what);
+  // step guard: this step's flag word lives behind the gradients (RNB_GRAD_TAIL); cleared here, ORed into by the blend kernel,
+  // the field backward and rnb_engine_grad_check, read by the Adam kernels
+  int32_t* flags = with_backward ? reinterpret_cast<int32_t*>(grads_f32 + c->n_params) : nullptr;
+  if (flags) RNB_CUDA(cudaMemsetAsync(flags, 0, 4, st), what);
   // 1. march all K passes (AABB inline), 2. scan, 3. expand -- unless the batch was marched ahead of time
   const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, c->scale);
   const dim3 ray_grid(ceil_div((int64_t)R * 32, 256), K);
@@ -579,6 +612,7 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   B.rgb = (float*)(ws + L.rgb); B.opacity = (float*)(ws + L.opacity); B.depth = (float*)(ws + L.depth);
   B.d_opacity = (float*)(ws + L.d_pass_opacity); B.d_depth = (float*)(ws + L.d_pass_depth); B.d_rgb = (float*)(ws + L.d_pass_rgb);
   B.dlogits = (__half*)(ws + L.gate_dlogits); B.loss = (float*)(ws + L.loss); B.with_backward = with_backward;
+  B.seg = seg; B.flags = flags; B.status = (int32_t*)(ws + L.status);
   float* dsig = (float*)(ws + L.dsigmas); float* drgb = (float*)(ws + L.drgbs);
   { StageTimer tm(ST_COMP_FW, st);
   eng_composite_fw_kernel<<<ray_grid, 256, 0, st>>>(sigmas, rgb4, deltas, ts, counts, starts, c->T_threshold, R, S, wsamp, p_op, p_de, p_rgb,
@@ -598,7 +632,7 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   float* gg[RNB_MAX_K]; float* gr[RNB_MAX_K];
   for (int i = 0; i < K; i++) { gg[i] = grads_f32 + c->geo_off[i]; gr[i] = grads_f32 + c->rgb_off[i]; }
   { StageTimer tm(ST_FIELD_BW, st);
-  if (int rc = rnb_field_bwd(&P, &Sm, &Sv, rgb4, dsig, drgb, c->loss_scale, grads_f32 + c->table_off, gg, gr, stream)) return rc; }
+  if (int rc = rnb_field_bwd_guarded(&P, &Sm, &Sv, rgb4, dsig, drgb, c->loss_scale, grads_f32 + c->table_off, gg, gr, flags, stream)) return rc; }
   if (K > 1 && !skip_gate_bwd) return rnb_engine_gate_bwd(c, workspace, params_f16, grads_f32, stream);
   return RNB_OK;
 }
@@ -611,20 +645,45 @@ int rnb_engine_fwd_bwd(const rnb_engine_config* c, void* workspace, const void* 
                                importance, with_backward, march_slot, nullptr, nullptr, 0, stream);
 }
 
-int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq, int64_t n,
-                    float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale, rnb_stream_t stream) {
-  const char* what = "rnb_engine_adam";
-  RNB_REQUIRE(params_f32 && params_f16 && grads_f32 && exp_avg && exp_avg_sq && n > 0 && step >= 1, what);
+static int launch_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                       float beta1, float beta2, float eps, int64_t step, float grad_scale, const int32_t* flags, int32_t* status,
+                       rnb_stream_t stream, const char* what) {
+  RNB_REQUIRE(params_f32 && params_f16 && grads_f32 && exp_avg && exp_avg_sq && n > 0, what);
   RNB_REQUIRE(((uintptr_t)params_f32 & 15) == 0 && ((uintptr_t)grads_f32 & 15) == 0 && ((uintptr_t)exp_avg & 15) == 0 &&
               ((uintptr_t)exp_avg_sq & 15) == 0 && ((uintptr_t)params_f16 & 7) == 0, what);
-  const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
-  const float step_size = (float)(lr / bc1), inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
   int64_t blocks = (n / 4 + 255) / 256;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;      // (a single resident wave, 5 blocks per SM, measured 3 % slower)
   if (blocks < 1) blocks = 1;
   StageTimer tm(ST_ADAM, as_stream(stream));
-  eng_adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(params_f32, (__half*)params_f16, grads_f32, exp_avg, exp_avg_sq, n, step_size,
-                                                              beta1, beta2, eps, inv_sqrt_bc2, grad_scale);
+  eng_adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(params_f32, (__half*)params_f16, grads_f32, exp_avg, exp_avg_sq, n, lr, step,
+                                                              beta1, beta2, eps, grad_scale, flags, status);
+  return check_launch(what);
+}
+
+int rnb_engine_adam(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq, int64_t n,
+                    float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale, rnb_stream_t stream) {
+  const char* what = "rnb_engine_adam";
+  RNB_REQUIRE(step >= 1, what);
+  return launch_adam(params_f32, params_f16, grads_f32, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, step, grad_scale, nullptr, nullptr,
+                     stream, what);
+}
+
+int rnb_engine_adam_guarded(float* params_f32, void* params_f16, float* grads_f32, float* exp_avg, float* exp_avg_sq, int64_t n,
+                            float lr, float beta1, float beta2, float eps, float grad_scale, const int32_t* flags, int32_t* status,
+                            rnb_stream_t stream) {
+  const char* what = "rnb_engine_adam_guarded";
+  RNB_REQUIRE(flags != nullptr && status != nullptr, what);
+  return launch_adam(params_f32, params_f16, grads_f32, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, 1, grad_scale, flags, status,
+                     stream, what);
+}
+
+int rnb_engine_grad_check(const float* grads_f32, int64_t lo, int64_t hi, int32_t* flags, rnb_stream_t stream) {
+  const char* what = "rnb_engine_grad_check";
+  RNB_REQUIRE(grads_f32 && flags && lo >= 0 && hi >= lo, what);
+  if (hi == lo) return RNB_OK;
+  int64_t blocks = (hi - lo + 1023) / 1024;
+  if (blocks > kNumSMs) blocks = kNumSMs;
+  eng_grad_check_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(grads_f32, lo, hi, flags);
   return check_launch(what);
 }
 

@@ -555,7 +555,12 @@ __device__ __forceinline__ void tc_mask_row64(uint32_t taddr, uint2 mask, unsign
   }
 }
 
-__device__ __forceinline__ float tc_sat_h(float v) { return fminf(fmaxf(v, -65504.f), 65504.f); }
+// gradient seeds enter the fp16 chain saturated; `bad` records that one did not fit (or is nan): the step guard then
+// skips the optimizer step, as the reference's GradScaler does for an inf (train_ml.py:304)
+__device__ __forceinline__ float tc_sat_h(float v, bool& bad) {
+  bad |= !(fabsf(v) <= 65504.f);
+  return fminf(fmaxf(v, -65504.f), 65504.f);
+}
 
 // weight-gradient accumulator (M = 64: row i lives in TMEM lane 32*(i/16) + i%16) -> global fp32 gradient
 template <int N>
@@ -581,7 +586,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
     TcFieldArgs A, const __half* __restrict__ s_enc, const __half* __restrict__ s_rgb_in, const __half* __restrict__ s_geo_h,
     const __half* __restrict__ s_rgb_h1, const __half* __restrict__ s_rgb_h2, const __half* __restrict__ s_sraw,
     const __half* __restrict__ rgb4, const float* __restrict__ dsig, const float* __restrict__ drgb, float gs,
-    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels, int agg_long_res) {
+    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels, int agg_long_res, int32_t* __restrict__ flags) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool is_issuer = warp == kWGB * 4;
@@ -717,6 +722,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
       for (int64_t n = 0; n < my_tiles; n++) {
         const int64_t s = base + (t0 + n * tile_stride) * kRows + row;
         const bool valid = s < pass_end;
+        bool bad = false;
         // ---- step 0: rgb layer 3 (sigmoid): dZ = dL/drgb * gs * y (1 - y) ----
         {
           uint4 q = make_uint4(0u, 0u, 0u, 0u);
@@ -725,8 +731,8 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
             const float2 y01 = __half22float2(*reinterpret_cast<const __half2*>(&yq.x));
             const float2 y23 = __half22float2(*reinterpret_cast<const __half2*>(&yq.y));
             const float d0 = __ldg(drgb + 3 * s), d1 = __ldg(drgb + 3 * s + 1), d2 = __ldg(drgb + 3 * s + 2);
-            q.x = pack2h(tc_sat_h(d0 * gs * y01.x * (1.f - y01.x)), tc_sat_h(d1 * gs * y01.y * (1.f - y01.y)));
-            q.y = pack2h(tc_sat_h(d2 * gs * y23.x * (1.f - y23.x)), 0.f);
+            q.x = pack2h(tc_sat_h(d0 * gs * y01.x * (1.f - y01.x), bad), tc_sat_h(d1 * gs * y01.y * (1.f - y01.y), bad));
+            q.y = pack2h(tc_sat_h(d2 * gs * y23.x * (1.f - y23.x), bad), 0.f);
           }
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 0)) = q;
           *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
@@ -748,7 +754,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
         float dsr = 0.f;
         if (valid) {   // TruncExp backward: g * exp(clamp(x, -15, 15))  (custom_functions.py:170-173)
           const float raw = __half2float(s_sraw[s]);
-          dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)));
+          dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)), bad);
         }
         tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
         if (row == 0) issue_load(n, 4, q_load + 1);
@@ -792,10 +798,16 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           // the activation gradient is carried in fp16 like the operator path: round, park the row in this
           // thread's (now idle) dz row so that the level loop below stays rolled (small code, no I-cache misses)
 #pragma unroll
-          for (int c = 0; c < 4; c++)
-            *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, c)) =
-                make_uint4(pack2h(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])), pack2h(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3])),
-                           pack2h(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])), pack2h(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7])));
+          for (int c = 0; c < 4; c++) {
+            const uint4 q = make_uint4(pack2h(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])), pack2h(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3])),
+                                       pack2h(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])), pack2h(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7])));
+            *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, c)) = q;
+            // an inf / nan in d(encoding) (an overflow anywhere up the fp16 chain ends here) would reach the table gradient
+            const uint32_t e = (q.x & 0x7c007c00u) ^ 0x7c007c00u, f = (q.y & 0x7c007c00u) ^ 0x7c007c00u;
+            const uint32_t g2 = (q.z & 0x7c007c00u) ^ 0x7c007c00u, h = (q.w & 0x7c007c00u) ^ 0x7c007c00u;
+            bad |= valid && (!(e & 0xffffu) || !(e >> 16) || !(f & 0xffffu) || !(f >> 16) || !(g2 & 0xffffu) || !(g2 >> 16) || !(h & 0xffffu) || !(h >> 16));
+          }
+          if (flags != nullptr && __any_sync(kFullMask, bad) && lane == 0) atomicOr(flags, RNB_FLAG_NONFINITE);
           // the per-level constants are indexed loads from the parameter bank (~100+ cycles each, and the loop is rolled):
           // level l + 1's are fetched while level l is processed
           float sc_n = A.g.scale[0];
@@ -858,11 +870,25 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
 
 using namespace rnb;
 
-int rnb_field_fwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, float* sigmas,
-                            void* rgb4_f16, rnb_stream_t stream) {
-  const char* what = "rnb_field_fwd(tcgen05)";
-  TcFieldArgs A;
+// argument checks shared by the entry points (the kernels are specialised for L = 16 levels, F = 2: 32 features)
+static int check_field_args(const rnb_field_params* P, const rnb_samples* S, const char* what) {
   RNB_REQUIRE(P != nullptr && S != nullptr && P->K >= 1 && P->K <= RNB_MAX_K && P->grid.n_levels == 16, what);
+  RNB_REQUIRE(P->table_f16 != nullptr, what);
+  for (int i = 0; i < P->K; i++) RNB_REQUIRE(P->geo_w_f16[i] && P->rgb_w_f16[i], what);
+  RNB_REQUIRE(S->rays_o && S->rays_d && S->ray_id && S->ts && S->seg, what);
+  RNB_REQUIRE(S->capacity > 0 && S->capacity % kRows == 0, what);
+  return RNB_OK;
+}
+
+extern "C" {
+
+int rnb_field_fwd(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, float* sigmas,
+                  void* rgb4_f16, rnb_stream_t stream) {
+  const char* what = "rnb_field_fwd";
+  TcFieldArgs A;
+  if (int rc = check_field_args(P, S, what)) return rc;
+  RNB_REQUIRE(sigmas && rgb4_f16, what);
+  if (saved != nullptr && saved->enc != nullptr) RNB_REQUIRE(saved->rgb_in && saved->geo_h && saved->rgb_h1 && saved->rgb_h2 && saved->sraw, what);
   if (int rc = to_levels(&P->grid, &A.g, what)) return rc;
   for (int c = 0; c < 3; c++) { A.xmin[c] = P->xyz_min[c]; A.xden[c] = P->xyz_max[c] - P->xyz_min[c]; }
   A.table = (const __half2*)P->table_f16;
@@ -889,12 +915,15 @@ int rnb_field_fwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   return check_launch(what);
 }
 
-int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, const void* rgb4_f16,
-                            const float* dL_dsigmas, const float* dL_drgbs, float loss_scale, float* grad_table,
-                            float* const* grad_geo, float* const* grad_rgb, rnb_stream_t stream) {
-  const char* what = "rnb_field_bwd(tcgen05)";
+int rnb_field_bwd_guarded(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, const void* rgb4_f16,
+                          const float* dL_dsigmas, const float* dL_drgbs, float loss_scale, float* grad_table,
+                          float* const* grad_geo, float* const* grad_rgb, int32_t* flags, rnb_stream_t stream) {
+  const char* what = "rnb_field_bwd";
   TcFieldArgs A;
-  RNB_REQUIRE(P != nullptr && S != nullptr && P->K >= 1 && P->K <= RNB_MAX_K && P->grid.n_levels == 16, what);
+  if (int rc = check_field_args(P, S, what)) return rc;
+  RNB_REQUIRE(saved && saved->enc && saved->rgb_in && saved->geo_h && saved->rgb_h1 && saved->rgb_h2 && saved->sraw, what);
+  RNB_REQUIRE(rgb4_f16 && dL_dsigmas && dL_drgbs && grad_table && grad_geo && grad_rgb && loss_scale > 0.f, what);
+  for (int i = 0; i < P->K; i++) RNB_REQUIRE(grad_geo[i] && grad_rgb[i], what);
   if (int rc = to_levels(&P->grid, &A.g, what)) return rc;
   for (int c = 0; c < 3; c++) { A.xmin[c] = P->xyz_min[c]; A.xden[c] = P->xyz_max[c] - P->xyz_min[c]; }
   A.table = (const __half2*)P->table_f16;
@@ -932,9 +961,17 @@ int rnb_field_bwd_tc_launch(const rnb_field_params* P, const rnb_samples* S, con
   field_bwd_tc_kernel<<<grid, kWGB * 128 + 32, TcBwdSmem::bytes, as_stream(stream)>>>(
       A, (const __half*)saved->enc, (const __half*)saved->rgb_in, (const __half*)saved->geo_h, (const __half*)saved->rgb_h1,
       (const __half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg,
-      agg_long_res);
+      agg_long_res, flags);
   return check_launch(what);
 }
+
+int rnb_field_bwd(const rnb_field_params* P, const rnb_samples* S, const rnb_field_saved* saved, const void* rgb4_f16,
+                  const float* dL_dsigmas, const float* dL_drgbs, float loss_scale, float* grad_table,
+                  float* const* grad_geo, float* const* grad_rgb, rnb_stream_t stream) {
+  return rnb_field_bwd_guarded(P, S, saved, rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, grad_geo, grad_rgb, nullptr, stream);
+}
+
+}  // extern "C"
 
 // Density of grid cells for rnb_grid_update (grid.cu).  span/half: per-cascade scalars computed by the caller.
 int rnb_density_cells_tc_launch(const rnb_field_params* P, float* const* tmp, int C, int G, int64_t M, const float* span, const float* half,

@@ -16,7 +16,7 @@
 // CUDA IPC handle) and mapped into the other processes with rnb_peer_open.
 #include <string.h>
 
-#include "common.cuh"
+#include "adam.cuh"
 
 namespace rnb {
 
@@ -73,15 +73,29 @@ __device__ __forceinline__ uint2 to_half4(float4 pp) {
 template <int W>
 __global__ void __launch_bounds__(256) adam_sharded_kernel(PeerPtrs P, int world, int rank, float* __restrict__ p32, float* __restrict__ m,
                                                            float* __restrict__ v, int64_t lo4, int64_t hi4, int64_t rep_lo4, int64_t rep_hi4,
-                                                           float* __restrict__ zero_buf, int64_t zero_n4, float step_size, float beta1,
-                                                           float beta2, float eps, float inv_sqrt_bc2, float grad_scale) {
+                                                           float* __restrict__ zero_buf, int64_t zero_n4, float lr, int64_t host_step,
+                                                           float beta1, float beta2, float eps, float grad_scale, int64_t flag_index,
+                                                           int32_t* __restrict__ status) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float4 g[W];
   int64_t i = lo4 + t0;
   if (i < hi4) load_peers<W>(P, world, i, g);
+  // step guard: OR of every rank's flag word (peer loads) -> all ranks skip or apply the same step
+  int flag_bits = 0;
+  if (flag_index >= 0 && threadIdx.x == 0) {
+#pragma unroll
+    for (int p = 0; p < W; p++)
+      if (p < world) flag_bits |= *reinterpret_cast<const volatile int32_t*>(P.grads[p] + flag_index);
+  }
+  __shared__ AdamStep sh;
+  adam_prologue(&sh, flag_bits, status, host_step, lr, beta1, beta2);
+  const float step_size = sh.step_size, inv_sqrt_bc2 = sh.inv_sqrt_bc2;
   if (zero_buf != nullptr)
     for (int64_t z = t0; z < zero_n4; z += stride) __stcs(reinterpret_cast<float4*>(zero_buf) + z, make_float4(0.f, 0.f, 0.f, 0.f));
+  // skipped step: nothing is applied.  The gradient buffer the peers are reading now is cleared by the NEXT step's kernel
+  // like any other (zero_buf alternation), so there is nothing else to do.
+  if (sh.skip) return;
   for (; i < hi4; i += stride) {
     float4 gn[W];
     const bool more = i + stride < hi4;
@@ -153,10 +167,10 @@ int rnb_adam_shard_bounds(int64_t n, int rank, int world, int64_t* lo, int64_t* 
   return RNB_OK;
 }
 
-int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers, float* params_f32,
-                            float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded, float* zero_grads, float lr, float beta1,
-                            float beta2, float eps, int64_t step, float grad_scale, rnb_stream_t stream) {
-  const char* what = "rnb_engine_adam_sharded";
+static int launch_adam_sharded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers, float* params_f32,
+                               float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded, float* zero_grads, float lr, float beta1,
+                               float beta2, float eps, int64_t step, float grad_scale, int64_t flag_index, int32_t* status,
+                               rnb_stream_t stream, const char* what) {
   RNB_REQUIRE(world >= 1 && world <= RNB_MAX_PEERS && rank >= 0 && rank < world && grads_peers && params_f16_peers, what);
   RNB_REQUIRE(params_f32 && exp_avg && exp_avg_sq && n > 0 && n % 4 == 0 && step >= 1, what);
   RNB_REQUIRE(n_sharded > 0 && n_sharded <= n && n_sharded % 4 == 0 && ((uintptr_t)zero_grads & 15) == 0, what);
@@ -169,8 +183,6 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
   }
   int64_t lo, hi;
   if (int rc = rnb_adam_shard_bounds(n_sharded, rank, world, &lo, &hi)) return rc;
-  const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
-  const float step_size = (float)(lr / bc1), inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
   // instantiation width: the smallest of 2 / 4 / 8 peers that holds `world` (RNB_PEER_MIN_WIDTH: test hook that runs the
   // wider instantiations on a box with fewer GPUs, tests/test_multi_gpu.py)
   int width = world <= 2 ? 2 : world <= 4 ? 4 : RNB_MAX_PEERS;
@@ -186,13 +198,30 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
   if (blocks < 1) blocks = 1;
 #define RNB_LAUNCH_ADAM_SHARDED(W)                                                                                                   \
   adam_sharded_kernel<W><<<(int)blocks, 256, 0, as_stream(stream)>>>(P, world, rank, params_f32, exp_avg, exp_avg_sq, lo / 4, hi / 4,   \
-                                                                    n_sharded / 4, n / 4, zero_grads, n / 4, step_size, beta1, beta2,   \
-                                                                    eps, inv_sqrt_bc2, grad_scale)
+                                                                    n_sharded / 4, n / 4, zero_grads, n / 4, lr, step, beta1, beta2,    \
+                                                                    eps, grad_scale, flag_index, status)
   if (width == 2) RNB_LAUNCH_ADAM_SHARDED(2);
   else if (width == 4) RNB_LAUNCH_ADAM_SHARDED(4);
   else RNB_LAUNCH_ADAM_SHARDED(RNB_MAX_PEERS);
 #undef RNB_LAUNCH_ADAM_SHARDED
   return check_launch(what);
+}
+
+int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers, float* params_f32,
+                            float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded, float* zero_grads, float lr, float beta1,
+                            float beta2, float eps, int64_t step, float grad_scale, rnb_stream_t stream) {
+  return launch_adam_sharded(rank, world, grads_peers, params_f16_peers, params_f32, exp_avg, exp_avg_sq, n, n_sharded, zero_grads, lr,
+                             beta1, beta2, eps, step, grad_scale, -1, nullptr, stream, "rnb_engine_adam_sharded");
+}
+
+int rnb_engine_adam_sharded_guarded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers,
+                                    float* params_f32, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded,
+                                    float* zero_grads, float lr, float beta1, float beta2, float eps, float grad_scale,
+                                    int32_t* status, rnb_stream_t stream) {
+  const char* what = "rnb_engine_adam_sharded_guarded";
+  RNB_REQUIRE(status != nullptr, what);
+  return launch_adam_sharded(rank, world, grads_peers, params_f16_peers, params_f32, exp_avg, exp_avg_sq, n, n_sharded, zero_grads, lr,
+                             beta1, beta2, eps, 1, grad_scale, n, status, stream, what);
 }
 
 }  // extern "C"

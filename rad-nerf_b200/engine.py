@@ -39,7 +39,14 @@ class _Config(ctypes.Structure):
 _LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_hidden", "gate_logits", "gate_dlogits", "gate_prob", "dgate", "importance",
                   "t_scratch", "counts", "starts", "seg", "ray_id", "ts", "deltas", "enc", "rgb_in", "geo_h", "rgb_h1", "rgb_h2",
                   "sraw", "sigmas", "rgb4", "ws", "dsigmas", "drgbs", "pass_opacity", "pass_depth", "pass_rgb", "pass_total",
-                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss", "march_slot1", "march_slot_bytes", "coarse"]
+                  "d_pass_opacity", "d_pass_depth", "d_pass_rgb", "rgb", "opacity", "depth", "loss", "march_slot1", "march_slot_bytes", "coarse",
+                  "status"]
+
+GRAD_TAIL = 64      # RNB_GRAD_TAIL: floats behind the gradients; word [n_params] is the step guard's flag word
+
+
+class SampleCapacityError(_lib.RadNerfB200Error):
+    """A step's samples did not fit the workspace (`samples_per_ray`); the step was skipped on the device."""
 
 
 class _Layout(ctypes.Structure):
@@ -77,7 +84,13 @@ class _Span:
 class Engine:
     def __init__(self, model, gate=None, n_rays=8192, exp_step_factor=0.0, samples_per_ray=128, max_samples=1024,
                  T_threshold=1e-4, near_distance=0.01, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
-                 loss_scale=128.0 * 1024.0, lr=1e-2, betas=(0.9, 0.999), eps=1e-15, sharded_optimizer=True):
+                 loss_scale=128.0 * 1024.0, lr=1e-2, betas=(0.9, 0.999), eps=1e-15, sharded_optimizer=True,
+                 on_overflow="raise", dynamic_loss_scale=True, growth_interval=2000):
+        """on_overflow: what happens when a step's samples exceed the workspace (n_rays * K * samples_per_ray): the
+        device skips that optimizer step either way (its tail samples were dropped, so its gradient is biased);
+        "raise" -> SampleCapacityError at the next step boundary, "grow" -> the workspace is re-allocated with headroom
+        and training continues.  dynamic_loss_scale: GradScaler policy of the reference's precision=16 run
+        (train_ml.py:304): halve on a skipped non-finite step, double after `growth_interval` applied steps."""
         _lib.lib()
         self.model, self.gate = model, gate
         self.K = K = getattr(model, "size", 1)
@@ -105,14 +118,16 @@ class Engine:
         if self.sharded:
             # buffers the other ranks address over NVLink (csrc/peer.cu): gradients are read, fp16 parameters written
             # (two alternating gradient buffers: the one peers read in step n is cleared by this rank's kernel of step n+1)
-            self._peer_g = [parallel.PeerBuffer(off * 4, dev), parallel.PeerBuffer(off * 4, dev)]
+            # (+ GRAD_TAIL floats: the step guard's flag word, which the peers' optimizer kernels read too)
+            self._peer_g = [parallel.PeerBuffer((off + GRAD_TAIL) * 4, dev), parallel.PeerBuffer((off + GRAD_TAIL) * 4, dev)]
             self._peer_p = parallel.PeerBuffer(off * 2, dev)
             self._g = 0
-            self.grads = self._peer_g[0].local.view(torch.float32)
+            self._grad_buf = self._peer_g[0].local.view(torch.float32)
             self.flat16 = self._peer_p.local.view(torch.float16)
         else:
             self.flat16 = torch.zeros(off, dtype=torch.float16, device=dev)
-            self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
+            self._grad_buf = torch.zeros(off + GRAD_TAIL, dtype=torch.float32, device=dev)
+        self.grads = self._grad_buf[:off]
         self.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
         self._mods = mods
@@ -141,10 +156,30 @@ class Engine:
             c.geo_off[i], c.rgb_off[i] = offs[f"geo{i}"], offs[f"rgb{i}"]
         c.gate_off = offs.get("gate", 0)
         self.cfg = c
+        self.samples_per_ray = int(samples_per_ray)
+        self.on_overflow = on_overflow
+        assert on_overflow in ("raise", "grow")
+        self.dynamic_loss_scale, self.growth_interval = bool(dynamic_loss_scale), int(growth_interval)
+        self._status_seen = [0, 0, 0, 0]          # host copy of the status counters last acted upon
+        self._status_ring = None                  # pinned read-back slots + events (no host synchronisation per step)
+        self._good_since_growth = 0
+        self._alloc_workspace()
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.opt_step = 0
+        # marching ahead (rnb_engine_march): the next batch's samples are produced on a side stream into the other slot
+        self._march_stream = None
+        self._gate_stream = None        # gate forward / backward next to the compositing kernels (forward_backward)
+        self.overlap_gate = os.environ.get("RNB_NO_GATE_OVERLAP", "0") != "1"
+        self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
+        self._slot = 0                  # slot holding the samples of the batch last trained on
+
+    def _alloc_workspace(self):
+        """Carve the workspace for cfg.sample_capacity and (re)create the tensor views of its regions."""
+        c, K = self.cfg, self.K
         L = _Layout()
         call("rnb_engine_layout_of", ctypes.byref(c), ctypes.byref(L))
         self.layout = L
-        self.ws = torch.empty(L.total_bytes, dtype=torch.uint8, device=dev)
+        self.ws = torch.empty(L.total_bytes, dtype=torch.uint8, device=self.device)
         R, S = self.n_rays, c.sample_capacity
         v = self._view
         self.gate_prob = v("gate_prob", torch.float32, (R, K))
@@ -157,14 +192,10 @@ class Engine:
         self.pass_depth = v("pass_depth", torch.float32, (K, R)); self.pass_total = v("pass_total", torch.int32, (K, R))
         self.rgb = v("rgb", torch.float32, (R, 3)); self.opacity = v("opacity", torch.float32, (R,)); self.depth = v("depth", torch.float32, (R, K))
         self.loss = v("loss", torch.float32, (8,))
-        self.lr, self.betas, self.eps = lr, betas, eps
-        self.opt_step = 0
-        # marching ahead (rnb_engine_march): the next batch's samples are produced on a side stream into the other slot
-        self._march_stream = None
-        self._gate_stream = None        # gate forward / backward next to the compositing kernels (forward_backward)
-        self.overlap_gate = os.environ.get("RNB_NO_GATE_OVERLAP", "0") != "1"
-        self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
-        self._slot = 0                  # slot holding the samples of the batch last trained on
+        self.status = v("status", torch.int32, (8,))
+        self.status.zero_()
+        if any(self._status_seen):        # re-allocation (capacity growth): carry the counters over
+            self.status[:4] = torch.tensor(self._status_seen, dtype=torch.int32, device=self.device)
 
     def _view(self, name, dtype, shape):
         off = getattr(self.layout, name)
@@ -235,6 +266,8 @@ class Engine:
         for t, n in ((rays_o, "rays_o"), (rays_d, "rays_d"), (target_rgb, "target_rgb")):
             _lib.check_input(t, n, torch.float32)
         assert rays_o.shape[0] == self.n_rays
+        self.sync_params()      # cheap version check: fp32 parameters changed through torch (load_state_dict) -> fp16 copies
+        self._poll_guard()      # act on the status the device reported for earlier steps (loss scale, capacity)
         cur = torch.cuda.current_stream(self.device)
         hit = self._ahead.pop((rays_o.data_ptr(), rays_d.data_ptr()), None)
         if hit is not None:
@@ -282,6 +315,7 @@ class Engine:
         bfs = self.bitfields()
         bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
         bg_arr = (ctypes.c_float * (3 * self.K))(*[float(x) for row in bg for x in row])
+        self._last_bg = [[float(x) for x in row] for row in bg]
         if inline:
             call("rnb_engine_march", ctypes.byref(c), self.ws, rays_o, rays_d, noise, bf_arr, i32(march_slot), st)
             _lib.launch_count -= 3
@@ -297,37 +331,119 @@ class Engine:
         if side_bwd:
             with torch.cuda.stream(self._gate_stream):
                 self._gate_stream.wait_event(blend_evt)
-                call("rnb_engine_gate_bwd", ctypes.byref(c), self.ws, self.flat16, self.grads, stream_arg(self.device))
+                call("rnb_engine_gate_bwd", ctypes.byref(c), self.ws, self.flat16, self._grad_buf, stream_arg(self.device))
                 joined = torch.cuda.Event(); joined.record(self._gate_stream)
             cur.wait_event(joined)            # whatever follows on the step's stream (the optimizer) sees the gate gradients
 
     def adam_step(self, lr=None):
+        """Optimizer step behind the step guard: an inf / nan in the dense networks' gradients is looked for here
+        (rnb_engine_grad_check; the table gradient and the fp16 seeds are checked where they are produced), then the
+        Adam kernel applies the step -- or, when the flag word is set on ANY rank, clears the gradients and leaves
+        parameters and moments alone.  The count of applied steps (for the bias corrections) lives on the device."""
         self.opt_step += 1
+        n = self.n_params
+        flags = self._grad_buf[n:]
+        mlp_lo = self.offsets["geo0"]
+        call("rnb_engine_grad_check", self._grad_buf, i64(mlp_lo), i64(n), flags, stream_arg(self.device))
         if self.sharded:
             # one kernel: this rank's shard of sum_p grads_p (peer loads) -> Adam -> fp16 parameters into every rank's buffer
             # (peer stores); the gate block is updated redundantly on every rank; the previous step's gradient buffer is
-            # cleared.  The stream barrier in front orders it after every rank's backward.  Behind it, the next step's gate
-            # forward touches only this rank's own gate replica and the importance all-reduce that follows it completes only
-            # once every rank has left this kernel -- for K = 1 there is no such all-reduce, so a second barrier is issued.
+            # cleared.  The stream barrier in front orders it after every rank's backward (and gradient check).  Behind it a
+            # second barrier keeps every rank's next step (field kernels, occupancy update, rendering: all readers of the
+            # fp16 parameters) behind every peer's parameter stores.
             sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             cur, prev = self._peer_g[self._g], self._peer_g[self._g ^ 1]
             n_sharded = self.offsets["gate"] if self.K > 1 else self.n_params
             sp = _Span(_Span.ADAM, self.device)
-            call("rnb_engine_adam_sharded", i32(parallel.rank()), i32(self.world), cur.pointer_array(),
+            call("rnb_engine_adam_sharded_guarded", i32(parallel.rank()), i32(self.world), cur.pointer_array(),
                  self._peer_p.pointer_array(), self.flat, self.exp_avg, self.exp_avg_sq, i64(self.n_params), i64(n_sharded),
                  prev.local, f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps),
-                 i64(self.opt_step), f32(1.0), stream_arg(self.device))
+                 f32(1.0), self.status, stream_arg(self.device))
             sp.end()
-            if self.K == 1 or self.overlap_gate:
-                sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
+            sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             self._g ^= 1
-            self.grads = self._peer_g[self._g].local.view(torch.float32)      # (cleared by the kernel of the previous step)
+            self._grad_buf = self._peer_g[self._g].local.view(torch.float32)      # (cleared by the kernel of the previous step)
+            self.grads = self._grad_buf[:n]
             self._master_stale = True
+        else:
+            parallel.allreduce_sum_(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
+            if self.world > 1:                       # ... and every rank must take the same skip decision
+                dist.all_reduce(flags[:1].view(torch.int32), op=dist.ReduceOp.MAX)
+            call("rnb_engine_adam_guarded", self.flat, self.flat16, self._grad_buf, self.exp_avg, self.exp_avg_sq, i64(n),
+                 f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), f32(1.0),
+                 flags, self.status, stream_arg(self.device))
+        self._post_status()
+
+    # -- step guard: host side ---------------------------------------------------------------------------------
+    def _post_status(self):
+        """Asynchronous read-back of the status counters into a pinned ring; consumed by _poll_guard one or more steps
+        later (the host never waits for the device here)."""
+        if self._status_ring is None:
+            self._status_ring = {"pin": torch.zeros(4, 8, dtype=torch.int32).pin_memory(), "evt": [None] * 4, "k": 0,
+                                 "stream": torch.cuda.Stream(self.device)}
+        r = self._status_ring
+        k = r["k"] % 4
+        done = torch.cuda.Event(); done.record(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(r["stream"]):
+            r["stream"].wait_event(done)
+            r["pin"][k].copy_(self.status, non_blocking=True)
+            ev = torch.cuda.Event(); ev.record(r["stream"]); r["evt"][k] = ev
+        r["k"] += 1
+
+    def _poll_guard(self, wait=False):
+        r = self._status_ring
+        if r is None:
             return
-        parallel.allreduce_sum_(self.grads)      # loss terms are normalised by the GLOBAL ray count: a plain sum is the gradient
-        call("rnb_engine_adam", self.flat, self.flat16, self.grads, self.exp_avg, self.exp_avg_sq, i64(self.n_params),
-             f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), i64(self.opt_step),
-             f32(1.0), stream_arg(self.device))
+        newest = None
+        for j in range(r["k"] - 1, max(r["k"] - 5, -1), -1):       # newest finished slot
+            ev = r["evt"][j % 4]
+            if ev is None:
+                continue
+            if wait:
+                ev.synchronize()
+            if ev.query():
+                newest = r["pin"][j % 4].tolist()
+                break
+        if newest is None:
+            return
+        skipped_inf, skipped_cap, needed, applied = newest[:4]
+        seen = self._status_seen
+        d_inf, d_cap, d_app = skipped_inf - seen[0], skipped_cap - seen[1], applied - seen[3]
+        self._status_seen = [skipped_inf, skipped_cap, needed, applied]
+        if self.dynamic_loss_scale:
+            if d_inf > 0:        # GradScaler: backoff_factor 0.5 per skipped step
+                self.cfg.loss_scale = max(self.cfg.loss_scale * 0.5 ** d_inf, 1.0)
+                self._good_since_growth = 0
+            elif d_app > 0:
+                self._good_since_growth += d_app
+                if self._good_since_growth >= self.growth_interval:      # growth_factor 2 every growth_interval clean steps
+                    self.cfg.loss_scale = min(self.cfg.loss_scale * 2.0, 2.0 ** 24)
+                    self._good_since_growth = 0
+        if d_cap > 0:
+            cap = self.cfg.sample_capacity
+            if self.on_overflow == "raise":
+                raise SampleCapacityError(
+                    f"{d_cap} training step(s) needed up to {needed} samples but the workspace holds {cap} "
+                    f"(n_rays {self.n_rays} x K {self.K} x samples_per_ray {self.samples_per_ray}); those optimizer steps "
+                    f"were skipped on the device.  Re-create the Engine with samples_per_ray >= "
+                    f"{-(-needed // (self.n_rays * self.K)) + 1} or on_overflow='grow'.")
+            self.grow(int(needed * 1.25))
+
+    def grow(self, min_capacity):
+        """Re-allocate the workspace for at least `min_capacity` samples (on_overflow='grow')."""
+        torch.cuda.synchronize(self.device)
+        self._ahead.clear()
+        self.cfg.sample_capacity = (max(int(min_capacity), self.cfg.sample_capacity) + 127) // 128 * 128
+        self.samples_per_ray = self.cfg.sample_capacity // (self.n_rays * self.K)
+        self._alloc_workspace()
+        self._render_cache = None
+
+    def guard_status(self):
+        """{'skipped_nonfinite', 'skipped_capacity', 'max_samples_needed', 'applied', 'loss_scale'} -- synchronises."""
+        torch.cuda.synchronize(self.device)
+        s = self.status.tolist()
+        return {"skipped_nonfinite": s[0], "skipped_capacity": s[1], "max_samples_needed": s[2], "applied": s[3],
+                "loss_scale": float(self.cfg.loss_scale)}
 
     def gather_master(self):
         """Sharded optimizer: fp32 master parameters and Adam moments are current only inside each rank's own shard.
@@ -361,11 +477,20 @@ class Engine:
     def results(self):
         """The reference's ml_render result dict (ml_rendering.py:72-77) as views of the workspace."""
         out = {"rgb": self.rgb, "depth": self.depth, "opacity": self.opacity,
-               "independent_rgbs": None, "pass_rgb": self.pass_rgb, "pass_opacity": self.pass_opacity}
+               "independent_rgbs": self.independent_rgbs(), "pass_rgb": self.pass_rgb, "pass_opacity": self.pass_opacity}
         if self.K > 1:
             out["gating_code"] = self.gate_prob
             out["gating_importance"] = self.importance
         return out
+
+    def independent_rgbs(self):
+        """The K per-sub-NeRF images AFTER the background blend (ml_rendering.py:46, 65, 73: `independent_rgbs`).  The
+        workspace keeps the composited colour and opacity of every pass before the blend, so this is
+        rgb_i + bg_i (1 - opacity_i), formed lazily (K small elementwise ops; not part of the timed step)."""
+        bg = torch.tensor(self._last_bg, dtype=torch.float32, device=self.device) if getattr(self, "_last_bg", None) else None
+        if bg is None:
+            return None
+        return [self.pass_rgb[i] + bg[i][None, :] * (1.0 - self.pass_opacity[i])[:, None] for i in range(self.K)]
 
     # -- occupancy grids ------------------------------------------------------------------------------------
     def grids(self):
@@ -446,7 +571,8 @@ class Engine:
             if K > 1:
                 gating[a:a + n] = ws[L.gate_prob:L.gate_prob + n * K * 4].view(torch.float32).view(n, K)
             total += stats[0]; rounds += stats[1]
-        out = {"rgb": rgb, "depth": depth, "opacity": opacity, "total_samples": total, "rounds": rounds, "independent_rgbs": None}
+        out = {"rgb": rgb, "depth": depth, "opacity": opacity, "total_samples": total, "rounds": rounds,
+               "independent_rgbs": [pass_rgb[i] for i in range(K)] if with_pass_rgb else None}     # ml_rendering.py:46, 65, 73
         if with_pass_rgb:
             out["pass_rgb"] = pass_rgb
         if K > 1:

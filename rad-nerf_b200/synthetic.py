@@ -198,6 +198,8 @@ def full_image_rays(cam: Cameras, img_idx: int = 0, rows: slice | None = None):
 
 # named workload shapes (BASELINE.json configs / SURVEY 8d)
 WORKLOADS = {
+    # BASELINE.json configs[0]: Instant-NGP volume-render FORWARD (AABB + march + composite), NSVF-style bounded scene, K = 1
+    "ngp_nsvf_k1_cpu_fwd": dict(scale=0.5, K=1, H=800, W=800, fx=1111.1, radius=1.5, forward_only=True),
     "ngp_blender_k1": dict(scale=0.5, K=1, H=800, W=800, fx=1111.1, radius=1.5),
     "radnerf_tat_k2": dict(scale=0.5, K=2, H=1080, W=1920, fx=1166.0, radius=0.9),   # radius tuned: ~33 samples/ray
     "radnerf_360_k4": dict(scale=16.0, K=4, H=822, W=1237, fx=1050.0, radius=1.0),

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 
 import numpy as np
 import torch
@@ -35,18 +36,54 @@ class _MlpDesc(ctypes.Structure):
                 ("n_hidden", ctypes.c_int32), ("out_activation", ctypes.c_int32)]
 
 
-def grid_meta(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale):
+_LIBM = None
+
+
+def _libm():
+    global _LIBM
+    if _LIBM is None:
+        _LIBM = ctypes.CDLL("libm.so.6")
+        for f in ("exp2f", "log2f", "ceilf"):
+            getattr(_LIBM, f).restype = ctypes.c_float
+            getattr(_LIBM, f).argtypes = [ctypes.c_float]
+    return _LIBM
+
+
+def level_scale_res(level, per_level_scale, base_resolution, rule="tcnn_fp32"):
+    """(scale_l, res_l) of one level.
+
+    rule "tcnn_fp32" (default) mirrors tinycudann's host arithmetic (grid.h grid_scale / grid_resolution, called from
+    the GridEncodingTemplated constructor with std::log2(float)): everything in fp32 through the C library --
+    exp2f(l * log2f(b)) * N_min - 1.0f, then (uint32)ceilf(scale) + 1.  This is the table a reference checkpoint's flat
+    `params` vector was laid out with.  rule "fp64_snap" is round 1's rule (fp64, snapped to 6 decimals): it differs
+    exactly where the real-valued scale is an integer -- at scene scale 0.5 (b = 64^(1/15)) levels 5, 10, 15 come out as
+    64 / 256 / 1024 instead of tinycudann's 65 / 257 / 1025, because fp32(b) rounds up and log2f returns 0.40000004."""
+    if rule == "fp64_snap":
+        s = round(2.0 ** (level * math.log2(per_level_scale)) * base_resolution - 1.0, 6)
+        return s, int(math.ceil(s)) + 1
+    assert rule == "tcnn_fp32", rule
+    m = _libm()
+    f = np.float32
+    log2b = f(m.log2f(ctypes.c_float(f(per_level_scale))))
+    e = f(f(level) * log2b)
+    s = f(f(f(m.exp2f(ctypes.c_float(e))) * f(base_resolution)) - f(1.0))
+    return float(s), int(m.ceilf(ctypes.c_float(s))) + 1
+
+
+def default_level_rule():
+    return os.environ.get("RNB_GRID_LEVEL_RULE", "tcnn_fp32")
+
+
+def grid_meta(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale, rule=None):
     """Level table of the multiresolution grid (tinycudann grid.h): scale_l = N_min*b^l - 1,
-    res_l = ceil(scale_l)+1, entries_l = min(round_up(res_l^3, 8), 2^log2_T).  The scale is
-    evaluated in fp64 and snapped (6 decimals) so that integer-valued levels do not depend on
-    libm rounding ("grid level rule")."""
+    res_l = ceil(scale_l)+1, entries_l = min(round_up(res_l^3, 8), 2^log2_T); scale_l / res_l as
+    level_scale_res() evaluates them (tinycudann's fp32 host arithmetic unless RNB_GRID_LEVEL_RULE=fp64_snap)."""
+    rule = rule or default_level_rule()
     m = _GridMeta()
     m.n_levels, m.n_features = n_levels, n_features
-    log2b = math.log2(per_level_scale)
     off = 0
     for l in range(n_levels):
-        s = round(2.0 ** (l * log2b) * base_resolution - 1.0, 6)
-        r = int(math.ceil(s)) + 1
+        s, r = level_scale_res(l, per_level_scale, base_resolution, rule)
         n = min(r ** 3, 2 ** 31 - 1)
         n = (n + 7) // 8 * 8
         n = min(n, 1 << log2_hashmap_size)

@@ -33,7 +33,8 @@ def cosine_lr(base_lr, step, total_steps, eta_min_ratio=1.0 / 30):
 class Trainer:
     def __init__(self, scale=0.5, K=2, lr=1e-2, log2_T=19, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
                  loss_scale=1024.0, device="cuda", update_interval=16, warmup_steps=256, freeze_occupancy=False,
-                 random_bg=False, seed=0, engine=True, batch_rays=8192, samples_per_ray=128, total_steps=None):
+                 random_bg=False, seed=0, engine=True, batch_rays=8192, samples_per_ray=128, total_steps=None,
+                 on_overflow="grow"):
         self.device = torch.device(device)
         self.K, self.scale = K, scale
         self.exp_step_factor = syn.exp_step_factor_for_scale(scale)
@@ -66,7 +67,7 @@ class Trainer:
             from .engine import Engine
             self.engine = Engine(self.model, self.gate, n_rays=batch_rays, exp_step_factor=self.exp_step_factor,
                                  samples_per_ray=samples_per_ray, lambda_opacity=lambda_opacity, lambda_cv=lambda_cv,
-                                 lambda_dm=lambda_dm, lr=lr)
+                                 lambda_dm=lambda_dm, lr=lr, on_overflow=on_overflow)
 
     # -- occupancy ---------------------------------------------------------------------------
     def set_occupancy(self, bitfields):

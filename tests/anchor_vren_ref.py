@@ -39,7 +39,7 @@ def main():
 
     _, w = workload("radnerf_tat_k2")
     cam = syn.make_cameras(100, w["radius"], w["H"], w["W"], w["fx"])
-    for R in (8192, 8192 * 16):
+    for R in ((8192,) if "--training-shape-only" in sys.argv else (8192, 8192 * 16)):
         o, d, _, _ = syn.train_batch(cam, R, 42)
         o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
         sc = syn.make_scene(0.5, 1234)

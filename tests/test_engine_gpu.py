@@ -27,12 +27,25 @@ def _names(K):
 
 @pytest.mark.parametrize("cfg,K,grid_init,n", [("bounded", 2, 0.2, 1024), ("bounded", 2, 1e-4, 777), ("unbounded", 4, 0.2, 1024)])
 def test_engine_step_matches_oracle(cfg, K, grid_init, n):
+    scale, esf = CONFIGS[cfg]
+    cam = syn.make_cameras(100, 1.5 if scale <= 0.5 else 1.0)
+    _engine_vs_oracle(scale, esf, K, grid_init, n, cam, 256)
+
+
+@pytest.mark.parametrize("workload", ["radnerf_tat_k2", "radnerf_360_k4"])
+def test_engine_step_matches_oracle_at_bench_shape(workload):
+    """The very batch shape bench.py times (BASELINE.json configs 3 and 4): the workload's cameras (1920x1080 fx 1166
+    radius 0.9 / 1237x822 fx 1050 radius 1.0), 8192 rays, K = 2 / 4, against the CPU oracle of the whole step."""
+    w = syn.WORKLOADS[workload]
+    cam = syn.make_cameras(100, w["radius"], w["H"], w["W"], w["fx"])
+    _engine_vs_oracle(w["scale"], syn.exp_step_factor_for_scale(w["scale"]), w["K"], 0.2, 8192, cam, 128)
+
+
+def _engine_vs_oracle(scale, esf, K, grid_init, n, cam, samples_per_ray):
     from oracle import render_cpu as R
     from radnerf_b200.engine import Engine
-    scale, esf = CONFIGS[cfg]
     P, model, gate, bitfields = build(scale, K, grid_init)
-    eng = Engine(model, gate, n_rays=n, exp_step_factor=esf, samples_per_ray=256, loss_scale=128.0 * 1024.0)
-    cam = syn.make_cameras(100, 1.5 if scale <= 0.5 else 1.0)
+    eng = Engine(model, gate, n_rays=n, exp_step_factor=esf, samples_per_ray=samples_per_ray, loss_scale=128.0 * 1024.0)
     o, d, _, _ = syn.train_batch(cam, n, 42)
     target = np.random.RandomState(1).rand(n, 3).astype(np.float32)
     torch.manual_seed(5)

@@ -1,74 +1,106 @@
-"""Fused occupancy-grid update (rnb_grid_update, csrc/grid.cu + density_cells_tc_kernel) against the drop-in
-Python body of MNGP.update_density_grid (networks.py:374-409) evaluated with the SAME random inputs.
+"""Fused occupancy-grid update (rnb_grid_update, csrc/grid.cu + density_cells_tc_kernel) against the CPU ORACLE of
+MNGP.update_density_grid (oracle/render_cpu.update_density_grid, restating /root/reference/models/networks.py:330-409)
+fed the SAME random inputs (uniform cells, picks among the occupied cells, in-cell jitter).
 
-Bars: the cell lists (ordered compaction = torch.nonzero, morton codes, picks) are integer work and must match
-exactly -- checked through which cells change; densities go through fp16 MLPs: 1e-2 relative; the bitfield must be
-bit-exact packbits(grid, min(mean(grid > 0), threshold)) of the grid the kernel produced; the mean within 1e-5.
+Bars:
+  * cell lists (uniform cells by morton code, ordered compaction = torch.nonzero, picks): integer work, bit-exact
+    against the oracle's lists (read back from the workspace's cell_idx region);
+  * densities go through fp16 MLPs: <= 1e-2 relative against the oracle's;
+  * duplicate cells: the reference's index_put leaves the winner to the hardware, so the produced value must lie
+    between the smallest and the largest candidate the oracle computed for that cell;
+  * untouched / invisible (< 0) cells: exactly grid * decay / unchanged;
+  * the bitfield is bit-exact packbits (C oracle, pinned by the reference's golden vectors) of the grid the kernel
+    produced at min(mean(grid > 0), threshold); against the ORACLE's bitfield only cells whose density is within the
+    density tolerance of the threshold may differ.
 """
 import numpy as np
 import pytest
 import torch
 
+from oracle import render_cpu as R
+from oracle import vren_cpu as O
 from radnerf_b200 import synthetic as syn
 
 pytestmark = pytest.mark.gpu
 G = 128
 G3 = G ** 3
+TOL = 1e-2
 
 
-def _model(scale, K):
+def _model(scale, K, seed=0):
+    """product model + engine carrying the oracle's parameters"""
     from radnerf_b200.engine import Engine
     from radnerf_b200.models.networks import MNGP, Ray_Gate
-    torch.manual_seed(0)
+    P = R.FieldParams(scale, K, seed=seed, grid_init=0.5)
     model = MNGP(scale, size=K).cuda()
     gate = Ray_Gate(K).cuda()
     with torch.no_grad():
-        model.xyz_encoder.params.uniform_(-0.5, 0.5)
+        model.xyz_encoder.params.copy_(P.p["xyz_encoder.params"].cuda())
+        for i in range(K):
+            getattr(model, f"geo_net_{i}").params.copy_(P.p[f"geo_net_{i}.params"].cuda())
+            getattr(model, f"rgb_net_{i}").params.copy_(P.p[f"rgb_net_{i}.params"].cuda())
+        gate.encoder.params.copy_(P.p["gate.encoder.params"].cuda())
     eng = Engine(model, gate, n_rays=1024, exp_step_factor=syn.exp_step_factor_for_scale(scale))
-    return model, eng
+    return P, model, eng
 
 
-def _points(model, coords, c, noise):
-    s = min(2 ** (c - 1), model.scale)
-    half = s / G
-    return (coords / (G - 1) * 2 - 1) * (s - half) + (noise * 2 - 1) * half
+def _check_bitfield_and_mean(model, eng, i, thr, oracle=None):
+    mean = float(eng.grid_mean().cpu()[i])
+    g = getattr(model, f"density_grid_{i}").cpu().numpy()
+    ref_mean = float(g[g > 0].astype(np.float64).mean())
+    assert abs(mean - ref_mean) <= 1e-5 * ref_mean
+    bf = getattr(model, f"density_bitfield_{i}").cpu().numpy()
+    assert np.array_equal(bf, O.packbits(g, min(mean, thr)))                    # bit-exact for the produced grid
+    if oracle is not None:
+        assert abs(mean - oracle["mean"]) <= 1e-3 * oracle["mean"]
+        diff = np.unpackbits(bf ^ oracle["bitfield"], bitorder="little").astype(bool)   # bit k of byte n = cell 8n + k
+        if diff.any():
+            # only cells sitting on the threshold may differ: within the density tolerance of it, or -- duplicate cells,
+            # whose winner the reference leaves to the hardware -- with candidates on either side of it
+            t = oracle["thr"]
+            lo, hi = oracle["grid_lo"].reshape(-1)[diff], oracle["grid_hi"].reshape(-1)[diff]
+            near = (np.abs(lo - t) <= 2 * TOL * t) | (np.abs(hi - t) <= 2 * TOL * t)
+            straddle = (lo <= t * (1 + 2 * TOL)) & (hi >= t * (1 - 2 * TOL))
+            assert diff.mean() < 2e-3 and np.all(near | straddle), (diff.mean(), int((~(near | straddle)).sum()))
 
 
-def _check_bitfield_and_mean(model, eng, K, thr):
-    mean = eng.grid_mean().cpu()
-    for i in range(K):
-        g = getattr(model, f"density_grid_{i}")
-        ref_mean = float(g[g > 0].double().mean())
-        assert abs(float(mean[i]) - ref_mean) <= 1e-5 * ref_mean
-        exp = syn.packbits_np(g.cpu().numpy(), min(float(mean[i]), thr))
-        assert np.array_equal(getattr(model, f"density_bitfield_{i}").cpu().numpy(), exp)
+def _check_grid(g, before, o, decay=0.95):
+    """g: produced grid (C, G3); o: oracle result"""
+    neg = before < 0
+    assert np.array_equal(g[neg], before[neg])                                   # invisible cells stay
+    un = ~o["touched"] & ~neg
+    assert np.array_equal(g[un], (before * np.float32(decay))[un])               # untouched cells only decay
+    t = o["touched"] & ~neg
+    assert np.all(g[t] >= o["grid_lo"][t] * (1 - TOL)) and np.all(g[t] <= o["grid_hi"][t] * (1 + TOL))
+    single = t & (o["tmp_lo"] == o["tmp_hi"])                                    # one candidate: plain value comparison
+    rel = np.abs(g[single] - o["grid"][single]) / np.maximum(np.abs(o["grid"][single]), 1e-6)
+    assert rel.max() <= TOL, rel.max()
+    return float(rel.max())
 
 
-@pytest.mark.parametrize("scale", [0.5, 2.0])
-def test_grid_update_warmup(scale):
-    from radnerf_b200 import vren
-    K = 2
-    model, eng = _model(scale, K)
+def test_grid_update_warmup_vs_oracle():
+    K, scale = 2, 0.5
+    P, model, eng = _model(scale, K)
     C = model.cascades
     torch.manual_seed(1)
     noise = torch.rand(K, C, G3, 3, device="cuda")
     thr = syn.DENSITY_THRESHOLD
-    # reference: the drop-in Python path, cell m = morton index m
-    coords = vren.morton3D_invert(torch.arange(G3, dtype=torch.int32, device="cuda")).float()
-    expect = []
-    with torch.no_grad():
-        for i in range(K):
-            tmp = torch.zeros(C, G3, device="cuda")
-            for c in range(C):
-                tmp[c] = model.density(_points(model, coords, c, noise[i, c]), i)
-            g = getattr(model, f"density_grid_{i}")
-            expect.append(torch.where(g < 0, g, torch.maximum(g * 0.95, tmp)))
-    eng.update_grid(thr, warmup=True, noise=noise)
-    for i in range(K):
+    before = []
+    for i in range(K):          # a non-trivial starting grid: zeros, old densities and invisible (-1) cells (networks.py:397-400)
         g = getattr(model, f"density_grid_{i}")
-        rel = (g - expect[i]).abs() / expect[i].abs().clamp_min(1e-6)
-        assert float(rel.max()) < 1e-2, float(rel.max())
-    _check_bitfield_and_mean(model, eng, K, thr)
+        g.copy_(torch.rand(C, G3, device="cuda") * 3.0)
+        g[torch.rand(C, G3, device="cuda") < 0.3] = 0.0
+        g[torch.rand(C, G3, device="cuda") < 0.05] = -1.0
+        before.append(g.cpu().numpy().copy())
+    eng.update_grid(thr, warmup=True, noise=noise)
+    nz = noise.cpu().numpy()
+    for i in range(K):
+        o = R.update_density_grid(P, i, before[i], thr, True, nz[i])
+        g = getattr(model, f"density_grid_{i}").cpu().numpy()
+        assert o["touched"].all()
+        worst = _check_grid(g, before[i], o)
+        _check_bitfield_and_mean(model, eng, i, thr, o)
+        print(f"warm-up sub-NeRF {i}: max density rel err {worst:.2e}, mean {o['mean']:.4f}")
     # built-in generator: every cell of every cascade is touched, values are plausible densities
     for i in range(K):
         getattr(model, f"density_grid_{i}").zero_()
@@ -76,15 +108,15 @@ def test_grid_update_warmup(scale):
     for i in range(K):
         g = getattr(model, f"density_grid_{i}")
         assert bool((g > 0).all())
-        assert abs(float(g.mean()) - float(expect[i].mean())) < 0.05 * float(expect[i].mean())
-    _check_bitfield_and_mean(model, eng, K, thr)
+        _check_bitfield_and_mean(model, eng, i, thr)
 
 
-def test_grid_update_steady_state():
-    from radnerf_b200 import vren
-    K, scale = 2, 0.5
-    model, eng = _model(scale, K)
+@pytest.mark.parametrize("scale,check", [(0.5, (0, 1)), (16.0, (1,))])
+def test_grid_update_steady_state_vs_oracle(scale, check):
+    K = 2
+    P, model, eng = _model(scale, K)
     C = model.cascades
+    assert C == syn.cascades_for_scale(scale)
     eng.update_grid(1e9, warmup=True)                    # fill the grids
     thr = float(torch.quantile(model.density_grid_0[0, ::64], 0.9))    # ~10 % of the cells count as occupied
     M1 = G3 // 4
@@ -92,38 +124,40 @@ def test_grid_update_steady_state():
     coords1 = torch.randint(G, (K, C, M1, 3), dtype=torch.int32, device="cuda")
     pick_u = torch.rand(K, C, M1, device="cuda")
     noise = torch.rand(K, C, 2 * M1, 3, device="cuda")
-    before = [getattr(model, f"density_grid_{i}").clone() for i in range(K)]
-    lo, hi, touched = [], [], []
-    with torch.no_grad():
-        for i in range(K):
-            tl = torch.full((C, G3), float("inf"), device="cuda"); th = torch.zeros(C, G3, device="cuda")
-            tm = torch.zeros(C, G3, dtype=torch.bool, device="cuda")
-            for c in range(C):
-                idx1 = vren.morton3D(coords1[i, c]).long()
-                occ = torch.nonzero(before[i][c] > thr)[:, 0]
-                assert len(occ) > 1000
-                idx2 = occ[(pick_u[i, c] * len(occ)).long().clamp_max(len(occ) - 1)]
-                idx = torch.cat([idx1, idx2])
-                cc = torch.cat([coords1[i, c], vren.morton3D_invert(idx2.int())]).float()
-                sig = model.density(_points(model, cc, c, noise[i, c]), i)
-                tl[c].scatter_reduce_(0, idx, sig, "amin"); th[c].scatter_reduce_(0, idx, sig, "amax")
-                tm[c, idx] = True
-            lo.append(torch.where(tm, tl, torch.zeros_like(tl))); hi.append(th); touched.append(tm)
+    before = [getattr(model, f"density_grid_{i}").cpu().numpy().copy() for i in range(K)]
     eng.update_grid(thr, warmup=False, noise=noise, coords1=coords1, pick_u=pick_u)
-    for i in range(K):
-        g = getattr(model, f"density_grid_{i}")
-        # untouched cells only decay; touched cells take max(decayed, one of the candidate densities)
-        un = ~touched[i]
-        assert torch.equal(g[un], (before[i] * 0.95)[un])
-        low = torch.maximum(before[i] * 0.95, lo[i]); high = torch.maximum(before[i] * 0.95, hi[i])
-        t = touched[i]
-        assert bool((g[t] >= low[t] * (1 - 1e-2)).all()) and bool((g[t] <= high[t] * (1 + 1e-2)).all())
-    _check_bitfield_and_mean(model, eng, K, thr)
-    # the scratch grid is left at zero for the next update
     L = eng._grid_layout
+    cell_idx = eng._grid_ws[L.cell_idx:L.cell_idx + K * C * 2 * M1 * 4].view(torch.int32).view(K, C, 2 * M1).cpu().numpy()
+    for i in check:
+        o = R.update_density_grid(P, i, before[i], thr, False, noise[i].cpu().numpy(), coords1[i].cpu().numpy(), pick_u[i].cpu().numpy())
+        for c in range(C):
+            assert len(o["cells"][c]) == 2 * M1                                  # every cascade has occupied cells here
+            assert np.array_equal(cell_idx[i, c], o["cells"][c].astype(np.int32))   # the cell lists: bit-exact
+        g = getattr(model, f"density_grid_{i}").cpu().numpy()
+        worst = _check_grid(g, before[i], o)
+        _check_bitfield_and_mean(model, eng, i, thr, o)
+        print(f"steady state scale {scale} sub-NeRF {i}: {int(o['touched'].sum())} cells touched, max density rel err {worst:.2e}")
+    # the scratch grid is left at zero for the next update
     assert int(eng._grid_ws[L.tmp:L.tmp + K * C * G3 * 4].view(torch.float32).count_nonzero()) == 0
     eng.update_grid(thr, warmup=False)                        # built-in generator path runs
-    _check_bitfield_and_mean(model, eng, K, thr)
+    for i in range(K):
+        _check_bitfield_and_mean(model, eng, i, thr)
+
+
+def test_grid_update_no_occupied_cells_keeps_uniform_half():
+    """networks.py:362-371: with no cell above the threshold only the uniform cells are evaluated."""
+    K, scale = 2, 0.5
+    P, model, eng = _model(scale, K)
+    M1 = G3 // 4
+    torch.manual_seed(3)
+    coords1 = torch.randint(G, (K, 1, M1, 3), dtype=torch.int32, device="cuda")
+    pick_u = torch.rand(K, 1, M1, device="cuda")
+    noise = torch.rand(K, 1, 2 * M1, 3, device="cuda")
+    before = [getattr(model, f"density_grid_{i}").cpu().numpy().copy() for i in range(K)]      # all zero
+    eng.update_grid(1e9, warmup=False, noise=noise, coords1=coords1, pick_u=pick_u)
+    o = R.update_density_grid(P, 0, before[0], 1e9, False, noise[0].cpu().numpy(), coords1[0].cpu().numpy(), pick_u[0].cpu().numpy())
+    assert len(o["cells"][0]) == M1
+    _check_grid(model.density_grid_0.cpu().numpy(), before[0], o)
 
 
 def test_trainer_uses_fused_grid_update():

@@ -34,7 +34,8 @@ def test_grid_meta_matches_oracle(scale):
     cfg = grid_cfg(scale)
     m, n = tcnn.grid_meta(16, 2, 19, 16, cfg["per_level_scale"])
     om = T.GridMeta(per_level_scale=cfg["per_level_scale"])
-    assert n == om.n_entries == {0.5: 5710032, 16.0: 6811592}[scale]
+    # tinycudann's fp32 host rule (tests/test_level_table_cpu.py prints it beside the real-valued rule SURVEY 2.4 used)
+    assert n == om.n_entries == {0.5: 5722520, 16.0: 6811592}[scale]
     assert list(m.res[:16]) == om.res and list(m.offset[:17]) == om.offsets
     assert np.allclose(np.array(m.scale[:16]), np.array(om.scales), rtol=0, atol=0)
 
