@@ -515,6 +515,13 @@ int rnb_engine_profile_timeline(int32_t* stage, double* start_ms, double* end_ms
 int rnb_tc_probe(const void* X, const void* W, const void* Y, float* out1, float* out2, float* out3,
                  rnb_stream_t stream);
 
+/* Diagnostics: rate of scattered L2 accesses with the field kernels' own instructions at random entries of a table
+ * (csrc/microbench.cu; scripts/microbench_l2.py).  kind 0/1/2: red.global.add .f32 / .v2.f32 / .v4.f32 into `entries` x 8
+ * bytes; 3/4: ld.global.nc .b32 / .b64 from `entries` x 4 bytes.  Every active lane of blocks x 256 threads issues
+ * iters x 8 accesses; *ops_out = lane-level accesses issued. */
+int rnb_diag_l2_rate(int kind, void* table, int64_t entries, int iters, int active_lanes, int blocks, int64_t* ops_out,
+                     rnb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -144,13 +144,14 @@ __device__ __forceinline__ void tc_relu_row64(uint32_t taddr, unsigned char* til
 // before it issues (and commits) this step's MMAs, and everybody waits for those, so no extra signalling is needed
 // (one exception: rgb hidden 2 overwrites rgb hidden 1 in the epilogue of the SAME step, see there).
 template <bool kSave, int N, int KDIM>
-__device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint32_t a_smem, uint32_t w_smem, __half* save_tile) {
+__device__ __forceinline__ void tc_fwd_step(uint64_t* bar, uint32_t tmem_d, uint32_t a_smem, uint32_t w_smem, __half* save_tile, uint64_t l2_stream = 0) {
   if (kSave) tc::bulk_wait_read();
   tc::fence_after_sync();
   tc_layer_mma<N, KDIM>(tmem_d, a_smem, w_smem);
   tc::mma_commit(bar);
   if (kSave) {
-    tc::bulk_store(save_tile, a_smem, kRows * KDIM * 2);
+    if (l2_stream) tc::bulk_store_hint(save_tile, a_smem, kRows * KDIM * 2, l2_stream);
+    else tc::bulk_store(save_tile, a_smem, kRows * KDIM * 2);
     tc::bulk_commit();
   }
 }
@@ -159,7 +160,7 @@ template <bool kSave>
 __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __restrict__ s_enc, __half* __restrict__ s_rgb_in,
                                                                      __half* __restrict__ s_geo_h, __half* __restrict__ s_rgb_h1,
                                                                      __half* __restrict__ s_rgb_h2, __half* __restrict__ s_sraw,
-                                                                     float* __restrict__ sigmas, __half* __restrict__ rgb4) {
+                                                                     float* __restrict__ sigmas, __half* __restrict__ rgb4, uint64_t l2_stream) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, wg = tid >> 7, row = tid & 127, warp = tid >> 5;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::bars);
@@ -179,6 +180,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
   uint32_t phase = 0;
   const int K = A.K;
   int64_t tiles_before = 0;
+  if (kSave && l2_stream) l2_stream = tc::l2_evict_first_policy();
   for (int pass = 0; pass < K; pass++) {
     const int64_t base = __ldg(A.seg + pass);
     int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
@@ -253,7 +255,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::g1, s_enc + s * 32);
+      if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::g1, s_enc + s * 32, l2_stream);
       if (valid_next) {      // second hop of the next tile's lookups; lands while this tile runs its five layers
         if (!valid) { r_next = __ldg(A.ray_id + s_next); nt = __ldg(A.ts + s_next); }
         nox = __ldg(A.rays_o + 3 * r_next); noy = __ldg(A.rays_o + 3 * r_next + 1); noz = __ldg(A.rays_o + 3 * r_next + 2);
@@ -266,7 +268,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 32, 64>(bar, tmem_d, b16_s, w_s + TcSmem::g2, s_geo_h + s * 64);
+      if (row == 0) tc_fwd_step<kSave, 32, 64>(bar, tmem_d, b16_s, w_s + TcSmem::g2, s_geo_h + s * 64, l2_stream);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       {
@@ -293,7 +295,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::r1, s_rgb_in + s * 32);
+      if (row == 0) tc_fwd_step<kSave, 64, 32>(bar, tmem_d, a8_s, w_s + TcSmem::r1, s_rgb_in + s * 32, l2_stream);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       tc_relu_row64(tmem_row, b16, row);
@@ -301,7 +303,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 64, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r2, s_rgb_h1 + s * 64);
+      if (row == 0) tc_fwd_step<kSave, 64, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r2, s_rgb_h1 + s * 64, l2_stream);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       if (kSave) {
@@ -315,7 +317,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
       tc::fence_async_smem();
       tc::fence_before_sync();
       wg_sync(wg);
-      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64);
+      if (row == 0) tc_fwd_step<kSave, 16, 64>(bar, tmem_d, b16_s, w_s + TcSmem::r3, s_rgb_h2 + s * 64, l2_stream);
       tc::mbar_wait(bar, phase); phase ^= 1;
       tc::fence_after_sync();
       {
@@ -486,8 +488,23 @@ struct TcBwdSmem {
   static constexpr int per_wg = 3 * kRows * 64 * 2;
   static constexpr int bars = wg0 + kWGB * per_wg;                // full[kWGB], done[kWGB], loaded[kWGB][2]
   static constexpr int tmem_slot = bars + 4 * kWGB * 8;
-  static constexpr int bytes = tmem_slot + 16;
+  static constexpr int ready = tmem_slot + 16;                    // i32 [kWGB][4]: tiles of this pass whose d(encoding) rows were handed over
+  static constexpr int bytes = ready + kWGB * 4 * 4;
 };
+// Scatter warps.  The table scatter (16 levels x 8 corners of reductions per sample, plus the run aggregation on the
+// coarse levels) used to run in the compute warpgroups behind the five MMA round trips of a tile: a warp was either in its
+// MMA chain (mostly waiting) or in its scatter (latency-bound: ~1400 cycles per level and warp), never both (ncu r01: 27 %
+// occupancy, issue 36 %, nothing saturated).  It now runs in kScatterWarps dedicated warps of the same CTA: a compute warp
+// hands its 32 rows of d(encoding) (fp16) and the samples' positions over through the global-memory region of the tile's
+// own saved rgb-hidden-2 activations -- dead by then, L2-resident, 10 of its 16 KB -- publishes a counter in shared memory
+// and goes on with its next tile.  One region per tile: no slot reuse, so the compute warpgroups never wait for the
+// scatter.  Tried and dropped (profiles/r02_ab_bwd_scatter.txt): a CTA-wide queue of 4-level units that compute warps also
+// serve while their MMAs are in flight (0.43-0.48 ms: a stolen unit holds up the warpgroup's next MMA step, and every
+// unit pays the L2 latency of its inputs again), and redux.sync / match.any for the run sums (0.76 ms: both are slow with
+// partial masks).
+constexpr int kHandoffXyz = 16 * kRows * 4;                       // byte offset of float4 (x, y, z, valid)[128] behind half2 d[16][128]
+static_assert(kHandoffXyz + kRows * 16 <= kRows * 64 * 2, "the hand-off fits the tile's rgb-hidden-2 region");
+constexpr int bwd_threads(int scatter_warps) { return kWGB * 128 + scatter_warps * 32 + 32; }
 // TMEM columns: per-warpgroup dA accumulators, then the five persistent weight-gradient accumulators
 constexpr int kColD = 0, kColWg1 = 64 * kWGB, kColWg2 = kColWg1 + 32, kColWr1 = kColWg2 + 64, kColWr2 = kColWr1 + 32, kColWr3 = kColWr2 + 64;
 static_assert(kColWr3 + 64 <= 512, "TMEM budget");
@@ -582,15 +599,20 @@ __device__ __forceinline__ void tc_flush_wgrad(uint32_t tmem_cols, int n_out, fl
   }
 }
 
-__global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
+template <int kScatterWarps>
+__global__ void __launch_bounds__(bwd_threads(kScatterWarps), 1) field_bwd_tc_kernel(
     TcFieldArgs A, const __half* __restrict__ s_enc, const __half* __restrict__ s_rgb_in, const __half* __restrict__ s_geo_h,
-    const __half* __restrict__ s_rgb_h1, const __half* __restrict__ s_rgb_h2, const __half* __restrict__ s_sraw,
+    const __half* __restrict__ s_rgb_h1, __half* s_rgb_h2, const __half* __restrict__ s_sraw,
     const __half* __restrict__ rgb4, const float* __restrict__ dsig, const float* __restrict__ drgb, float gs,
-    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels, int agg_long_res, int32_t* __restrict__ flags) {
+    float* __restrict__ grad_table, TcGradPtrs G, int n_aggregate_levels, int agg_long_res, int32_t* __restrict__ flags, uint64_t l2_stream, int agg_half) {
   extern __shared__ __align__(128) unsigned char smem[];
+  constexpr int kBwdThreads = bwd_threads(kScatterWarps);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool is_issuer = warp == kWGB * 4;
+  const bool is_issuer = warp == kWGB * 4 + kScatterWarps;
+  const bool is_scatter = warp >= kWGB * 4 && !is_issuer;
   const int wg = tid >> 7, row = tid & 127;
+  volatile int32_t* ready = reinterpret_cast<volatile int32_t*>(smem + TcBwdSmem::ready);   // [g][w]: tiles of this pass handed over
+
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + TcBwdSmem::bars);
   uint64_t* done = full + kWGB;
   uint64_t* loaded = done + kWGB;          // [kWGB][2]: a saved-input tile has landed in buffer b of warpgroup g
@@ -607,11 +629,14 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
   const uint32_t tmem = *tmem_slot;
   const uint32_t w_s = tc::smem_u32(smem);
   const float inv_gs = 1.0f / gs;
+  if (l2_stream) l2_stream = tc::l2_evict_first_policy();
   const int K = A.K;
-  uint32_t ph_full[kWGB] = {0, 0, 0, 0};   // issuer-side parities
-  uint32_t in_buf[kWGB] = {0, 0, 0, 0};    // issuer-side: which saved-input buffer the next step of warpgroup g reads
-  uint32_t ph_done = 0;                    // warpgroup-side parity
-  uint32_t q_load = 0;                     // warpgroup-side: saved-input tiles consumed so far (buffer = q & 1, parity = (q >> 1) & 1)
+  // per-role state in two registers (the three roles share one register allocation):
+  //   issuer:    ra = parities of full[g] (bit g), rb = saved-input buffer the next step of warpgroup g reads (bit g)
+  //   warpgroup: ra = parity of done[wg],          rb = saved-input tiles consumed so far (buffer = q & 1, parity = (q >> 1) & 1)
+  uint32_t ra = 0, rb = 0;
+#define ph_done ra
+#define q_load rb
   int64_t tiles_before = 0;
   for (int pass = 0; pass < K; pass++) {
     const int64_t base = __ldg(A.seg + pass);
@@ -623,12 +648,13 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
     {
       const __half* gw = A.geo_w[pass];
       const __half* rw = A.rgb_w[pass];
-      tc_stage_weight(smem + TcSmem::g1, gw, 64, 32, tid, kWGB * 128 + 32);
-      tc_stage_weight(smem + TcSmem::g2, gw + 64 * 32, 32, 64, tid, kWGB * 128 + 32);
-      tc_stage_weight(smem + TcSmem::r1, rw, 64, 32, tid, kWGB * 128 + 32);
-      tc_stage_weight(smem + TcSmem::r2, rw + 64 * 32, 64, 64, tid, kWGB * 128 + 32);
-      tc_stage_weight(smem + TcSmem::r3, rw + 64 * 32 + 64 * 64, 16, 64, tid, kWGB * 128 + 32);
+      tc_stage_weight(smem + TcSmem::g1, gw, 64, 32, tid, kBwdThreads);
+      tc_stage_weight(smem + TcSmem::g2, gw + 64 * 32, 32, 64, tid, kBwdThreads);
+      tc_stage_weight(smem + TcSmem::r1, rw, 64, 32, tid, kBwdThreads);
+      tc_stage_weight(smem + TcSmem::r2, rw + 64 * 32, 64, 64, tid, kBwdThreads);
+      tc_stage_weight(smem + TcSmem::r3, rw + 64 * 32 + 64 * 64, 16, 64, tid, kBwdThreads);
     }
+    if (tid < kWGB * 4) ready[tid] = 0;
     tc::fence_async_smem();
     __syncthreads();
     // round-robin over the grid's warpgroups, each pass continuing where the previous one stopped (see the forward kernel)
@@ -656,12 +682,12 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
 #pragma unroll
           for (int g = 0; g < kWGB; g++) {
             if (left[g] == 0) continue;
-            if (!mbar_test(full + g, ph_full[g])) continue;
-            ph_full[g] ^= 1;
+            if (!mbar_test(full + g, (ra >> g) & 1u)) continue;
+            ra ^= 1u << g;
             tc::fence_after_sync();
             const uint32_t dz_s = w_s + TcBwdSmem::wg0 + g * TcBwdSmem::per_wg + TcBwdSmem::dz;
-            const uint32_t in_s = dz_s + TcBwdSmem::in + in_buf[g] * TcBwdSmem::in_bytes;
-            in_buf[g] ^= 1;
+            const uint32_t in_s = dz_s + TcBwdSmem::in + ((rb >> g) & 1u) * TcBwdSmem::in_bytes;
+            rb ^= 1u << g;
             const uint32_t d_t = tmem + kColD + g * 64;
             switch (step[g]) {
               case 0:   // rgb layer 3: dZ (.,16), In = h2
@@ -691,6 +717,63 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
         }
       }
       __syncwarp();
+    } else if (is_scatter) {
+      // ---------------- scatter warps ----------------
+      // Unit of work: 32 rows (one compute warp's share) of one tile.  Unit u = n * 16 + g * 4 + w is the w-th quarter of the
+      // n-th tile of warpgroup g in this pass; scatter warp j takes the units u = j (mod kScatterWarps) in ascending order
+      // and waits for each one's hand-over (the warpgroups advance at about the same pace, so in-order service costs little
+      // and needs no bookkeeping).
+      for (int u = warp - kWGB * 4; ; u += kScatterWarps) {
+        const int n = u >> 4, g = (u >> 2) & 3, w = u & 3;
+        if ((int64_t)n * tile_stride >= n_tiles) break;
+        const int64_t tile = wg_first(g) + (int64_t)n * tile_stride;
+        if (tile >= n_tiles) continue;
+        while (ready[g * 4 + w] <= n) __nanosleep(100);
+        __threadfence_block();                                   // acquire: the rows written before the counter was bumped
+        const char* hand = reinterpret_cast<const char*>(s_rgb_h2 + (base + tile * kRows) * 64);
+        const uint32_t* hd = reinterpret_cast<const uint32_t*>(hand) + w * 32 + lane;       // + 128 per level
+        // d(encoding) comes back from L2 (~700 cycles, about what a level takes): a ring of four keeps the loads of levels
+        // l + 1 .. l + 4 in flight.  The per-level constants are indexed loads from the parameter bank (~100 cycles): one ahead.
+        uint32_t d_a = __ldcg(hd), d_b = __ldcg(hd + kRows), d_c = __ldcg(hd + 2 * kRows), d_d = __ldcg(hd + 3 * kRows);
+        const float4 q = __ldcg(reinterpret_cast<const float4*>(hand + kHandoffXyz) + w * 32 + lane);
+        const bool valid = q.w != 0.f;
+        float sc_n = A.g.scale[0];
+        uint32_t res_n = A.g.res[0], off_n = A.g.offset[0], end_n = A.g.offset[1];
+#pragma unroll 1
+        for (int l = 0; l < 16; l++) {
+          const uint32_t off = off_n, res_l = res_n, end_l = end_n, dw = d_a;
+          const float sc_l = sc_n;
+          d_a = d_b; d_b = d_c; d_c = d_d;
+          if (l < 12) d_d = __ldcg(hd + (l + 4) * kRows);
+          if (l < 15) { sc_n = A.g.scale[l + 1]; res_n = A.g.res[l + 1]; off_n = end_l; end_n = A.g.offset[l + 2]; }
+          const LevelCorners L = level_corners(q.x, q.y, q.z, sc_l, res_l, end_l - off);
+          const float2 d = __half22float2(*reinterpret_cast<const __half2*>(&dw));
+          const float d0 = d.x * inv_gs, d1 = d.y * inv_gs;
+          float* gl = grad_table + 2 * (size_t)off;
+          if (l < n_aggregate_levels) {   // warp-uniform
+            if (agg_half) {
+              if (res_l <= (uint32_t)agg_long_res) scatter_level_aggregated_h2<5>(gl, L, *reinterpret_cast<const __half2*>(&dw), 32.f * inv_gs, valid);
+              else scatter_level_aggregated_h2<3>(gl, L, *reinterpret_cast<const __half2*>(&dw), 32.f * inv_gs, valid);
+            } else if (res_l <= (uint32_t)agg_long_res) scatter_level_aggregated<5>(gl, L, d0, d1, valid);
+            else scatter_level_aggregated<3>(gl, L, d0, d1, valid);
+          } else if (valid) {
+            // x-neighbour corners that share an aligned pair of entries (see tc_encode_level) take ONE 16-byte reduction
+#pragma unroll
+            for (int p = 0; p < 4; p++) {
+              const uint32_t ia = L.idx[2 * p], ib = L.idx[2 * p + 1];
+              const float wa = L.w[2 * p], wb = L.w[2 * p + 1];
+              if ((ia ^ ib) == 1u) {
+                const bool odd = ia & 1u;
+                const float lo_w = odd ? wb : wa, hi_w = odd ? wa : wb;
+                red_add_f32x4(gl + 2 * (size_t)(ia & ~1u), lo_w * d0, lo_w * d1, hi_w * d0, hi_w * d1);
+              } else {
+                red_add_f32x2(gl + 2 * (size_t)ia, wa * d0, wa * d1);
+                red_add_f32x2(gl + 2 * (size_t)ib, wb * d0, wb * d1);
+              }
+            }
+          }
+        }
+      }
     } else {
       // ---------------- warpgroups: thread = sample ----------------
       unsigned char* dzb = smem + TcBwdSmem::wg0 + wg * TcBwdSmem::per_wg + TcBwdSmem::dz;
@@ -710,7 +793,8 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
                                                                                                                             : s_enc + s0 * 32;
         const uint32_t bytes = (j == 2 || j == 4) ? kRows * 32 * 2 : kRows * 64 * 2;
         tc::mbar_expect_tx(ld + (q & 1), bytes);
-        tc::bulk_load(inb_s + (q & 1) * TcBwdSmem::in_bytes, src, bytes, ld + (q & 1));
+        if (l2_stream) tc::bulk_load_hint(inb_s + (q & 1) * TcBwdSmem::in_bytes, src, bytes, ld + (q & 1), l2_stream);
+        else tc::bulk_load(inb_s + (q & 1) * TcBwdSmem::in_bytes, src, bytes, ld + (q & 1));
       };
       auto wait_load = [&]() -> const unsigned char* {          // every thread: the tile of load q_load is in shared memory
         const unsigned char* p = inb + (q_load & 1) * TcBwdSmem::in_bytes;
@@ -718,6 +802,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
         q_load++;
         return p;
       };
+      auto wait_mma = [&]() { tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; };
       if (row == 0) { issue_load(0, 0, q_load); issue_load(0, 1, q_load + 1); }
       for (int64_t n = 0; n < my_tiles; n++) {
         const int64_t s = base + (t0 + n * tile_stride) * kRows + row;
@@ -739,13 +824,13 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
         }
         uint2 mask = tc_row_mask64(wait_load(), row);                                     // relu'(h2)
         tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
-        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        wait_mma(); tc::fence_after_sync();
         if (row == 0) issue_load(n, 2, q_load + 1);
         // ---- step 1: rgb layer 2 ----
         tc_mask_row64(tmem_row, mask, dzb, row);
         mask = tc_row_mask64(wait_load(), row);                                           // relu'(h1)
         tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
-        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        wait_mma(); tc::fence_after_sync();
         if (row == 0) issue_load(n, 3, q_load + 1);
         // ---- step 2: rgb layer 1 ----
         tc_mask_row64(tmem_row, mask, dzb, row);
@@ -756,7 +841,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           const float raw = __half2float(s_sraw[s]);
           dsr = tc_sat_h(__ldg(dsig + s) * gs * expf(fminf(fmaxf(raw, -15.f), 15.f)), bad);
         }
-        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        wait_mma(); tc::fence_after_sync();
         if (row == 0) issue_load(n, 4, q_load + 1);
         // ---- step 3: geo layer 2: dZ = [d raw sigma | d feature (16) | 0 ...] ----
         {
@@ -773,7 +858,7 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
         }
         mask = tc_row_mask64(wait_load(), row);                                           // relu'(geo hidden)
         tc::fence_async_smem(); tc::fence_before_sync(); tc::mbar_arrive(full + wg);
-        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        wait_mma(); tc::fence_after_sync();
         if (row == 0) issue_load(n + 1, 0, q_load + 1);                                   // next tile's first input
         // ---- step 4: geo layer 1 ----
         tc_mask_row64(tmem_row, mask, dzb, row);
@@ -787,60 +872,29 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
           y = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 1), t, __ldg(A.rays_o + 3 * ry + 1)) - A.xmin[1], A.xden[1]), 0.f), 1.f);
           z = fminf(fmaxf(__fdiv_rn(__fmaf_rn(__ldg(A.rays_d + 3 * ry + 2), t, __ldg(A.rays_o + 3 * ry + 2)) - A.xmin[2], A.xden[2]), 0.f), 1.f);
         }
-        tc::mbar_wait(done + wg, ph_done); ph_done ^= 1; tc::fence_after_sync();
+        wait_mma(); tc::fence_after_sync();
         if (row == 0) issue_load(n + 1, 1, q_load + 1);
-        // ---- step 5: d(encoding) row -> scatter into the fp32 table gradient ----
+        // ---- step 5: d(encoding) row (fp16, like the operator path) -> the scatter warps ----
         {
           uint32_t r[32];
           tc::tmem_ld32_nowait(tmem_row, r);
           tc::tmem_ld_wait();
           tc::fence_before_sync();
-          // the activation gradient is carried in fp16 like the operator path: round, park the row in this
-          // thread's (now idle) dz row so that the level loop below stays rolled (small code, no I-cache misses)
+          char* hand = reinterpret_cast<char*>(s_rgb_h2 + (s - row) * 64);      // this tile's rgb-hidden-2 region: consumed in steps 0 and 1
+          uint32_t* hd = reinterpret_cast<uint32_t*>(hand) + row;
 #pragma unroll
-          for (int c = 0; c < 4; c++) {
-            const uint4 q = make_uint4(pack2h(__uint_as_float(r[8 * c]), __uint_as_float(r[8 * c + 1])), pack2h(__uint_as_float(r[8 * c + 2]), __uint_as_float(r[8 * c + 3])),
-                                       pack2h(__uint_as_float(r[8 * c + 4]), __uint_as_float(r[8 * c + 5])), pack2h(__uint_as_float(r[8 * c + 6]), __uint_as_float(r[8 * c + 7])));
-            *reinterpret_cast<uint4*>(dzb + tc::tile_chunk_off(kRows, row, c)) = q;
-            // an inf / nan in d(encoding) (an overflow anywhere up the fp16 chain ends here) would reach the table gradient
-            const uint32_t e = (q.x & 0x7c007c00u) ^ 0x7c007c00u, f = (q.y & 0x7c007c00u) ^ 0x7c007c00u;
-            const uint32_t g2 = (q.z & 0x7c007c00u) ^ 0x7c007c00u, h = (q.w & 0x7c007c00u) ^ 0x7c007c00u;
-            bad |= valid && (!(e & 0xffffu) || !(e >> 16) || !(f & 0xffffu) || !(f >> 16) || !(g2 & 0xffffu) || !(g2 >> 16) || !(h & 0xffffu) || !(h >> 16));
-          }
-          if (flags != nullptr && __any_sync(kFullMask, bad) && lane == 0) atomicOr(flags, RNB_FLAG_NONFINITE);
-          // the per-level constants are indexed loads from the parameter bank (~100+ cycles each, and the loop is rolled):
-          // level l + 1's are fetched while level l is processed
-          float sc_n = A.g.scale[0];
-          uint32_t res_n = A.g.res[0], off_n = A.g.offset[0], end_n = A.g.offset[1];
-#pragma unroll 1
           for (int l = 0; l < 16; l++) {
-            const uint32_t off = off_n, res_l = res_n, end_l = end_n;
-            const float sc_l = sc_n;
-            if (l < 15) { sc_n = A.g.scale[l + 1]; res_n = A.g.res[l + 1]; off_n = end_l; end_n = A.g.offset[l + 2]; }
-            const LevelCorners L = level_corners(x, y, z, sc_l, res_l, end_l - off);
-            const float2 d = __half22float2(*reinterpret_cast<const __half2*>(dzb + tc::tile_chunk_off(kRows, row, l >> 2) + (l & 3) * 4));
-            const float d0 = d.x * inv_gs, d1 = d.y * inv_gs;
-            float* gl = grad_table + 2 * (size_t)off;
-            if (l < n_aggregate_levels) {   // warp-uniform
-              if (res_l <= (uint32_t)agg_long_res) scatter_level_aggregated<5>(gl, L, d0, d1, valid);
-              else scatter_level_aggregated<3>(gl, L, d0, d1, valid);
-            } else if (valid) {
-              // x-neighbour corners that share an aligned pair of entries (see tc_encode_level) take ONE 16-byte reduction
-#pragma unroll
-              for (int p = 0; p < 4; p++) {
-                const uint32_t ia = L.idx[2 * p], ib = L.idx[2 * p + 1];
-                const float wa = L.w[2 * p], wb = L.w[2 * p + 1];
-                if ((ia ^ ib) == 1u) {
-                  const bool odd = ia & 1u;
-                  const float lo_w = odd ? wb : wa, hi_w = odd ? wa : wb;
-                  red_add_f32x4(gl + 2 * (size_t)(ia & ~1u), lo_w * d0, lo_w * d1, hi_w * d0, hi_w * d1);
-                } else {
-                  red_add_f32x2(gl + 2 * (size_t)ia, wa * d0, wa * d1);
-                  red_add_f32x2(gl + 2 * (size_t)ib, wb * d0, wb * d1);
-                }
-              }
-            }
+            const uint32_t w = pack2h(__uint_as_float(r[2 * l]), __uint_as_float(r[2 * l + 1]));
+            // an inf / nan in d(encoding) (an overflow anywhere up the fp16 chain ends here) would reach the table gradient
+            const uint32_t e = (w & 0x7c007c00u) ^ 0x7c007c00u;
+            bad |= valid && (!(e & 0xffffu) || !(e >> 16));
+            __stcg(hd + l * kRows, w);                                         // warp: 128 contiguous bytes per level
           }
+          __stcg(reinterpret_cast<float4*>(hand + kHandoffXyz) + row, make_float4(x, y, z, valid ? 1.f : 0.f));
+          if (flags != nullptr && __any_sync(kFullMask, bad) && lane == 0) atomicOr(flags, RNB_FLAG_NONFINITE);
+          __threadfence_block();
+          __syncwarp();
+          if (lane == 0) ready[wg * 4 + (warp & 3)] = (int32_t)n + 1;
         }
       }
     }
@@ -864,11 +918,23 @@ __global__ void __launch_bounds__(kWGB * 128 + 32, 1) field_bwd_tc_kernel(
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
+#undef ph_done
+#undef q_load
 }
 
 }  // namespace rnb
 
 using namespace rnb;
+
+// L2 eviction policy of the saved-activation tiles.  They are written once by the forward kernel and read once by the backward
+// kernel, 260 MB per step -- twice the L2 -- and on their way through they push out what the kernels live off: the fp16
+// table (23 MB, gathered 128 times per sample) and the fp32 gradient table (46 MB, the target of every reduction; a
+// reduction that misses L2 waits for DRAM).  evict_first on the bulk copies keeps those resident.  RNB_L2_STREAM=0: off.
+static uint64_t l2_stream_policy() {
+  static int on = -1;
+  if (on < 0) { on = 1; if (const char* e = getenv("RNB_L2_STREAM")) on = atoi(e) != 0; }
+  return on ? 1ull : 0ull;        // (a flag: the kernels build the policy word themselves with createpolicy)
+}
 
 // argument checks shared by the entry points (the kernels are specialised for L = 16 levels, F = 2: 32 features)
 static int check_field_args(const rnb_field_params* P, const rnb_samples* S, const char* what) {
@@ -908,10 +974,10 @@ int rnb_field_fwd(const rnb_field_params* P, const rnb_samples* S, const rnb_fie
   if (save)
     field_fwd_tc_kernel<true><<<grid, kWG * 128, TcSmem::bytes, as_stream(stream)>>>(A, (__half*)saved->enc, (__half*)saved->rgb_in, (__half*)saved->geo_h,
                                                                                     (__half*)saved->rgb_h1, (__half*)saved->rgb_h2, (__half*)saved->sraw,
-                                                                                    sigmas, (__half*)rgb4_f16);
+                                                                                    sigmas, (__half*)rgb4_f16, l2_stream_policy());
   else
     field_fwd_tc_kernel<false><<<grid, kWG * 128, TcSmem::bytes, as_stream(stream)>>>(A, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, sigmas,
-                                                                                     (__half*)rgb4_f16);
+                                                                                     (__half*)rgb4_f16, 0);
   return check_launch(what);
 }
 
@@ -944,24 +1010,33 @@ int rnb_field_bwd_guarded(const rnb_field_params* P, const rnb_samples* S, const
   const float grow = fmaxf(1.0f, 1.3f * sqrtf(fmaxf(extent, 0.0f)));
   int n_agg = 0;
   for (int l = 0; l < A.g.n_levels; l++)
-    if ((float)A.g.res[l] <= 128.0f * grow) n_agg = l + 1;
+    if ((float)A.g.res[l] <= 340.0f * grow) n_agg = l + 1;      // (128 before the scatter moved to its own warps: there a combined level costs issue slots, not reductions)
   if (const char* e = getenv("RNB_AGG_LEVELS")) n_agg = atoi(e);   // tuning knob (profiles/): levels with warp-aggregated reductions
   if (n_agg > A.g.n_levels) n_agg = A.g.n_levels;
   while (n_agg > 0 && A.g.res[n_agg - 1] >= 1024) n_agg--;          // the cell key holds 10-11 bits per axis
   int agg_long_res = (int)(48.0f * grow);                           // levels up to this resolution combine whole-warp runs
   if (const char* e = getenv("RNB_AGG_LONG_RES")) agg_long_res = atoi(e);
-  static bool attr_set = false;
-  if (!attr_set) {
-    RNB_CUDA(cudaFuncSetAttribute(field_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcBwdSmem::bytes), what);
-    attr_set = true;
+  // scatter warps per CTA: 3 (20 warps, 96 registers) or 7 (24 warps, 80 registers) -- warps are allocated in fours, so a
+  // 21-warp CTA would be charged 24 (RNB_BWD_SCATTER_WARPS: A/B knob, profiles/)
+  static int n_scatter = 0, agg_half = 1;
+  if (n_scatter == 0) {
+    if (const char* e = getenv("RNB_AGG_HALF")) agg_half = atoi(e);      // run reduction on packed fp16 pairs (0: fp32, A/B)
+    n_scatter = 7;
+    if (const char* e = getenv("RNB_BWD_SCATTER_WARPS")) n_scatter = atoi(e) == 3 ? 3 : 7;
+    RNB_CUDA(cudaFuncSetAttribute(field_bwd_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcBwdSmem::bytes), what);
+    RNB_CUDA(cudaFuncSetAttribute(field_bwd_tc_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcBwdSmem::bytes), what);
   }
+  const uint64_t l2_stream = l2_stream_policy();
   const int64_t tiles = S->capacity / kRows;
   int grid = (int)((tiles + kWGB - 1) / kWGB);
   if (grid > kNumSMs) grid = kNumSMs;
-  field_bwd_tc_kernel<<<grid, kWGB * 128 + 32, TcBwdSmem::bytes, as_stream(stream)>>>(
-      A, (const __half*)saved->enc, (const __half*)saved->rgb_in, (const __half*)saved->geo_h, (const __half*)saved->rgb_h1,
-      (const __half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg,
-      agg_long_res, flags);
+#define RNB_LAUNCH_BWD(SW)                                                                                                              \
+  field_bwd_tc_kernel<SW><<<grid, bwd_threads(SW), TcBwdSmem::bytes, as_stream(stream)>>>(                                                \
+      A, (const __half*)saved->enc, (const __half*)saved->rgb_in, (const __half*)saved->geo_h, (const __half*)saved->rgb_h1,              \
+      (__half*)saved->rgb_h2, (const __half*)saved->sraw, (const __half*)rgb4_f16, dL_dsigmas, dL_drgbs, loss_scale, grad_table, G, n_agg, \
+      agg_long_res, flags, l2_stream, agg_half)
+  if (n_scatter == 7) RNB_LAUNCH_BWD(7); else RNB_LAUNCH_BWD(3);
+#undef RNB_LAUNCH_BWD
   return check_launch(what);
 }
 

@@ -165,19 +165,71 @@ __device__ __forceinline__ void scatter_level_aggregated(float* grad_level, cons
   const uint32_t prev = __shfl_up_sync(kFullMask, key, 1);
   const unsigned heads = __ballot_sync(kFullMask, lane == 0 || prev != key || (kSteps < 5 && (lane & ((1 << kSteps) - 1)) == 0));
   const unsigned after = (heads >> lane) >> 1;          // run heads strictly behind this lane
-  bool take[kSteps];
+  // Branch-free and corner-parallel: step j of all 16 values (8 corners x 2 features) is issued together -- 16 independent
+  // shuffles in flight -- and a lane that must not take its neighbour's partial sum adds 0 * v instead of branching around
+  // the add.  (The first form looped corner by corner with `if (take) g += v`: ncu showed the adds stalled on their own
+  // shuffle (short scoreboard) behind BSSY/BSYNC pairs, ~2700 cycles per level and warp.)
+  float m[kSteps];
 #pragma unroll
-  for (int j = 0; j < kSteps; j++) take[j] = lane + (1 << j) < 32 && (after & ((1u << (1 << j)) - 1u)) == 0u;
+  for (int j = 0; j < kSteps; j++) m[j] = (lane + (1 << j) < 32 && (after & ((1u << (1 << j)) - 1u)) == 0u) ? 1.f : 0.f;
   const bool emit = active && ((heads >> lane) & 1u);
+  float g0[8], g1[8];
 #pragma unroll
-  for (int k = 0; k < 8; k++) {
-    float g0 = L.w[k] * d0, g1 = L.w[k] * d1;
+  for (int k = 0; k < 8; k++) { g0[k] = active ? L.w[k] * d0 : 0.f; g1[k] = active ? L.w[k] * d1 : 0.f; }
 #pragma unroll
-    for (int j = 0; j < kSteps; j++) {
-      const float v0 = __shfl_down_sync(kFullMask, g0, 1 << j), v1 = __shfl_down_sync(kFullMask, g1, 1 << j);
-      if (take[j]) { g0 += v0; g1 += v1; }
+  for (int j = 0; j < kSteps; j++) {
+    float v0[8], v1[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { v0[k] = __shfl_down_sync(kFullMask, g0[k], 1 << j); v1[k] = __shfl_down_sync(kFullMask, g1[k], 1 << j); }
+#pragma unroll
+    for (int k = 0; k < 8; k++) { g0[k] = fmaf(m[j], v0[k], g0[k]); g1[k] = fmaf(m[j], v1[k], g1[k]); }
+  }
+  if (emit) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) red_add_f32x2(grad_level + 2 * (size_t)L.idx[k], g0[k], g1[k]);
+  }
+}
+
+// The same with the two features of a corner carried as ONE packed fp16 pair through the run reduction: half the shuffles
+// and adds (the reduction is what a scatter warp spends its issue slots on).  d is the fp16 pair the activation gradient is
+// carried in anyway (loss-scaled, so in fp16's range); it enters divided by 32 so that a 32-lane sum cannot overflow, the
+// run total leaves in fp32 times `mult` (= 32 / loss scale).  Rounding: each partial sum is rounded to fp16 (11 bits) -- the
+// table gradient agrees with the fp32 reduction to ~4e-4 L2-relative, against a 1e-2 gradient tolerance.
+template <int kSteps>
+__device__ __forceinline__ void scatter_level_aggregated_h2(float* grad_level, const LevelCorners& L, __half2 d, float mult, bool active) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t key = active ? L.cell : 0xffffffffu;
+  const uint32_t prev = __shfl_up_sync(kFullMask, key, 1);
+  const unsigned heads = __ballot_sync(kFullMask, lane == 0 || prev != key || (kSteps < 5 && (lane & ((1 << kSteps) - 1)) == 0));
+  const unsigned after = (heads >> lane) >> 1;          // run heads strictly behind this lane
+  __half2 m[kSteps];
+#pragma unroll
+  for (int j = 0; j < kSteps; j++) {
+    const float t = (lane + (1 << j) < 32 && (after & ((1u << (1 << j)) - 1u)) == 0u) ? 1.f : 0.f;
+    m[j] = __floats2half2_rn(t, t);
+  }
+  const bool emit = active && ((heads >> lane) & 1u);
+  const __half2 ds = active ? __hmul2(d, __floats2half2_rn(1.f / 32.f, 1.f / 32.f)) : __floats2half2_rn(0.f, 0.f);
+  __half2 g[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) g[k] = __hmul2(__float2half2_rn(L.w[k]), ds);
+#pragma unroll
+  for (int j = 0; j < kSteps; j++) {
+    __half2 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint32_t u = __shfl_down_sync(kFullMask, *reinterpret_cast<const uint32_t*>(&g[k]), 1 << j);
+      v[k] = *reinterpret_cast<const __half2*>(&u);
     }
-    if (emit) red_add_f32x2(grad_level + 2 * (size_t)L.idx[k], g0, g1);
+#pragma unroll
+    for (int k = 0; k < 8; k++) g[k] = __hfma2(m[j], v[k], g[k]);
+  }
+  if (emit) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const float2 f = __half22float2(g[k]);
+      red_add_f32x2(grad_level + 2 * (size_t)L.idx[k], f.x * mult, f.y * mult);
+    }
   }
 }
 

@@ -76,6 +76,22 @@ __device__ __forceinline__ void bulk_load(uint32_t sdst, const void* gsrc, uint3
                : "memory");
 }
 
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+// the same with an L2 cache-policy operand (createpolicy encoding, e.g. evict_first for data that is touched once)
+__device__ __forceinline__ void bulk_store_hint(void* gdst, uint32_t ssrc, uint32_t bytes, uint64_t policy) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(ssrc), "r"(bytes), "l"(policy)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_load_hint(uint32_t sdst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(sdst),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+               : "memory");
+}
+
 // ---- descriptors -----------------------------------------------------------------------------------
 // shared-memory matrix descriptor, no swizzle: start address, leading / stride byte offsets (16 B units), version 1
 __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {

@@ -163,6 +163,7 @@ class Engine:
         self._status_seen = [0, 0, 0, 0]          # host copy of the status counters last acted upon
         self._status_ring = None                  # pinned read-back slots + events (no host synchronisation per step)
         self._good_since_growth = 0
+        self.status_interval = 4                  # optimizer steps between two read-backs of the (cumulative) status counters
         self._alloc_workspace()
         self.lr, self.betas, self.eps = lr, betas, eps
         self.opt_step = 0
@@ -372,7 +373,8 @@ class Engine:
             call("rnb_engine_adam_guarded", self.flat, self.flat16, self._grad_buf, self.exp_avg, self.exp_avg_sq, i64(n),
                  f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), f32(1.0),
                  flags, self.status, stream_arg(self.device))
-        self._post_status()
+        if self.opt_step % self.status_interval == 0:
+            self._post_status()
 
     # -- step guard: host side ---------------------------------------------------------------------------------
     def _post_status(self):
@@ -391,6 +393,8 @@ class Engine:
         r["k"] += 1
 
     def _poll_guard(self, wait=False):
+        if wait:
+            self._post_status()
         r = self._status_ring
         if r is None:
             return
@@ -475,7 +479,8 @@ class Engine:
         return self.loss
 
     def results(self):
-        """The reference's ml_render result dict (ml_rendering.py:72-77) as views of the workspace."""
+        """The reference's ml_render result dict (ml_rendering.py:72-77) as views of the workspace ("independent_rgbs",
+        the K per-sub-NeRF images after the background blend, is formed when this is called: K small elementwise ops)."""
         out = {"rgb": self.rgb, "depth": self.depth, "opacity": self.opacity,
                "independent_rgbs": self.independent_rgbs(), "pass_rgb": self.pass_rgb, "pass_opacity": self.pass_opacity}
         if self.K > 1:
@@ -487,9 +492,15 @@ class Engine:
         """The K per-sub-NeRF images AFTER the background blend (ml_rendering.py:46, 65, 73: `independent_rgbs`).  The
         workspace keeps the composited colour and opacity of every pass before the blend, so this is
         rgb_i + bg_i (1 - opacity_i), formed lazily (K small elementwise ops; not part of the timed step)."""
-        bg = torch.tensor(self._last_bg, dtype=torch.float32, device=self.device) if getattr(self, "_last_bg", None) else None
-        if bg is None:
+        last = getattr(self, "_last_bg", None)
+        if last is None:
             return None
+        key = tuple(tuple(r) for r in last)
+        cache = getattr(self, "_bg_cache", None)
+        if cache is None or cache[0] != key:      # (the background only changes with --random_bg)
+            cache = (key, torch.tensor(last, dtype=torch.float32, device=self.device))
+            self._bg_cache = cache
+        bg = cache[1]
         return [self.pass_rgb[i] + bg[i][None, :] * (1.0 - self.pass_opacity[i])[:, None] for i in range(self.K)]
 
     # -- occupancy grids ------------------------------------------------------------------------------------

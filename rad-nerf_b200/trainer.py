@@ -108,6 +108,13 @@ class Trainer:
             self._shadow[n] = getattr(self.model, n)
             setattr(self.model, n, keep[n])
 
+    @property
+    def last_results(self):
+        """The reference's result dict of the last step (ml_rendering.py:72-77)."""
+        if getattr(self, "_last_results", None) is None and self.engine is not None:
+            self._last_results = self.engine.results()
+        return self._last_results
+
     # -- one step ----------------------------------------------------------------------------
     def step(self, rays_o, rays_d, target_rgb, next_rays=None):
         """rays_o, rays_d, target_rgb: (B_local,3) fp32 CUDA tensors.  Returns the (unscaled) loss tensor.
@@ -125,7 +132,7 @@ class Trainer:
                 next_rays = None
             loss = self.engine.step(rays_o, rays_d, target_rgb, lr=self.lr, random_bg=self.random_bg, next_rays=next_rays)
             self.global_step += 1
-            self.last_results = self.engine.results()
+            self._last_results = None             # formed on demand (Trainer.last_results): nothing per step on the host
             return loss[0]
         kw = dict(test_time=False, random_bg=self.random_bg)
         if self.exp_step_factor:
@@ -148,6 +155,6 @@ class Trainer:
             p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
         self.opt.step()
         self.global_step += 1
-        self.last_results = results
+        self._last_results = results
         self.last_loss = loss.detach()
         return self.last_loss

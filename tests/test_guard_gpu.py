@@ -81,20 +81,34 @@ def test_injected_nonfinite_gradient_is_skipped(where):
 
 
 def test_overflowing_fp16_chain_is_skipped():
-    """Weights arranged so that the FORWARD stays in range but the backward chain overflows fp16 between two layers
-    (rgb hidden layer scaled up by 1e5, the layer in front scaled down by 1e5): the inf lands in the weight gradients and
-    in d(encoding); the field backward's own check and rnb_engine_grad_check raise the flag (no planted values)."""
-    eng = _engine(loss_scale=128.0 * 1024.0, dynamic_loss_scale=False)
-    with torch.no_grad():
-        p = eng.model.rgb_net_0.params
-        p[:64 * 32].mul_(1e-5)
-        p[64 * 32:64 * 32 + 64 * 64].mul_(1e5)
+    """Weights arranged so that the FORWARD is unchanged but the backward chain overflows fp16 between two layers: the
+    geometry feature is scaled down by f where the geo network emits it and scaled back up by f where the rgb network reads
+    it, so d(feature) = dZ W_rgb1[:, 16:32] f leaves fp16's range.  The inf lands in the geo weight gradients and in
+    d(encoding); the field backward's own check and rnb_engine_grad_check raise the flag (no planted values), the step is
+    skipped.  The same loss scale with the original weights is applied cleanly first: it is not the seeds that saturate."""
     o, d, t = _batch(1024)
-    before = eng.flat.clone()
+    eng = _engine(loss_scale=2.0 ** 20, dynamic_loss_scale=False)
     eng.step(o, d, t)
-    st = eng.guard_status()
-    assert st["skipped_nonfinite"] == 1 and st["applied"] == 0
-    assert torch.equal(eng.flat, before) and float(eng.exp_avg.abs().max()) == 0.0
+    assert eng.guard_status()["applied"] == 1
+    loss_ref = float(eng.loss[0])
+    skipped = None
+    for f in (2.0 ** 10, 2.0 ** 13, 2.0 ** 16):
+        eng = _engine(loss_scale=2.0 ** 20, dynamic_loss_scale=False)
+        with torch.no_grad():
+            for i in range(2):
+                geo = getattr(eng.model, f"geo_net_{i}").params          # [W1 (64,32) | W2 (32,64)]: rows 1..16 of W2 emit the feature
+                geo[64 * 32 + 64:64 * 32 + 17 * 64].mul_(1.0 / f)
+                rgb = getattr(eng.model, f"rgb_net_{i}").params.view(-1)[:64 * 32].view(64, 32)   # W1 (64,32): columns 16..31 read it
+                rgb[:, 16:].mul_(f)
+        before = eng.flat.clone()
+        eng.step(o, d, t)
+        st = eng.guard_status()
+        assert abs(float(eng.loss[0]) - loss_ref) < 2e-2 * abs(loss_ref), (f, float(eng.loss[0]), loss_ref)   # same forward (fp16 rounding aside)
+        if st["skipped_nonfinite"] == 1:
+            skipped = f
+            assert st["applied"] == 0 and torch.equal(eng.flat, before) and float(eng.exp_avg.abs().max()) == 0.0
+            break
+    assert skipped is not None, "no factor made the backward chain overflow"
 
 
 def test_loss_scale_grows_after_clean_steps():
