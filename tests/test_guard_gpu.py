@@ -87,13 +87,13 @@ def test_overflowing_fp16_chain_is_skipped():
     d(encoding); the field backward's own check and rnb_engine_grad_check raise the flag (no planted values), the step is
     skipped.  The same loss scale with the original weights is applied cleanly first: it is not the seeds that saturate."""
     o, d, t = _batch(1024)
-    eng = _engine(loss_scale=2.0 ** 20, dynamic_loss_scale=False)
+    eng = _engine(loss_scale=2.0 ** 24, dynamic_loss_scale=False)
     eng.step(o, d, t)
     assert eng.guard_status()["applied"] == 1
     loss_ref = float(eng.loss[0])
     skipped = None
-    for f in (2.0 ** 10, 2.0 ** 13, 2.0 ** 16):
-        eng = _engine(loss_scale=2.0 ** 20, dynamic_loss_scale=False)
+    for f in (2.0 ** 12, 2.0 ** 14, 2.0 ** 16):
+        eng = _engine(loss_scale=2.0 ** 24, dynamic_loss_scale=False)
         with torch.no_grad():
             for i in range(2):
                 geo = getattr(eng.model, f"geo_net_{i}").params          # [W1 (64,32) | W2 (32,64)]: rows 1..16 of W2 emit the feature
