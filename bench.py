@@ -271,10 +271,12 @@ def run_product(args):
     from radnerf_b200.trainer import Trainer
     lib = _lib.lib()   # fail loudly if the CUDA library is missing: there is no fallback
     K = w["K"]
+    # weak scaling (default): 8192 rays per GPU; strong: a global batch of 8192 rays split over the ranks
+    batch = BATCH // world if args.scaling == "strong" else BATCH
     tr = Trainer(scale=w["scale"], K=K, freeze_occupancy=True, device=f"cuda:{local}", engine=not args.python_surface,
-                 batch_rays=BATCH)
+                 batch_rays=batch)
     tr.set_occupancy(scene_bitfields(syn, w))
-    host = [tuple(torch.from_numpy(a).pin_memory() for a in b) for b in make_batches(syn, w, rank)]
+    host = [tuple(torch.from_numpy(a).pin_memory() for a in b) for b in make_batches(syn, w, rank, batch=batch)]
     dev = [tuple(a.cuda(non_blocking=True) for a in b) for b in host]
     flush = torch.empty(256 * 1024 * 1024 // 4, device="cuda")      # 256 MiB > 126 MB L2
 
@@ -421,7 +423,7 @@ def run_product(args):
                    "flat16_checksum": [int(x) for x in allc[0][:2].tolist()],
                    "what": "fp16 parameter vector (two 64-bit checksums) and global gate importance equal on every rank after the timed steps"}
         assert same, f"replicas diverged: {[c.tolist() for c in allc]}"
-    rays_total = BATCH * world
+    rays_total = batch * world
     value = rays_total / (ms_step * 1e-3)
     e2e_val = rays_total / (e2e_ms * 1e-3)
     if rank != 0:
@@ -430,20 +432,21 @@ def run_product(args):
         return
     hbm, tflops, which = measured_peaks()
     line = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f16 (fp32 accumulate; fp32 march/composite)", "data": "synthetic",
             "config": arm_config(args, w, world),
-            "run": {"occupancy_update": "every 16 steps, on shadow grids (the marched occupancy stays the analytic scene's)",
+            "run": {"batch_rays_this_rank": batch,
+                    "occupancy_update": "every 16 steps, on shadow grids (the marched occupancy stays the analytic scene's)",
                     "march_ahead": bool(ahead),
                     "path": "fused engine (rnb_engine_*)" if tr.engine is not None else "python operator surface"},
             "ms_per_step_noflush": ms_noflush, "value_noflush": rays_total / (ms_noflush * 1e-3),
             "clocks": clk,
-            "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * BATCH * 12, "d2h_bytes_per_step": 32,
+            "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 3 * batch * 12, "d2h_bytes_per_step": 32,
                     "ms_per_step": e2e_ms},
             "gpu_launches": launches, "final_loss": losses[-1] if losses else None}
     if tr.engine is not None:
         counts, overflow = tr.engine.sample_stats()
-        N = float(sum(counts)); KR = float(K * BATCH); Pn = float(tr.engine.n_params)
+        N = float(sum(counts)); KR = float(K * batch); Pn = float(tr.engine.n_params)
         line["run"]["samples_per_ray"] = N / KR
         line["run"]["sample_overflow"] = overflow
         top = max(stage_ms, key=lambda k: stage_ms[k][0] * stage_ms[k][1])
@@ -603,6 +606,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="radnerf_tat_k2")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: 8192 rays per GPU (default); strong: a global batch of 8192 rays split over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-march-ahead", action="store_true", help="march every batch inside its own step (single stream)")
     ap.add_argument("--python-surface", action="store_true", help="time the drop-in Python operator surface instead of the fused engine")

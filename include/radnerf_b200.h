@@ -478,11 +478,18 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
                             float grad_scale, rnb_stream_t stream);
 /* The same behind the step guard (see RNB_GRAD_TAIL): every peer gradient buffer carries its flag word at float index n;
  * the kernel ORs all of them (peer loads), so every rank skips or applies the same step.  status: this rank's status
- * block (step count of applied steps as in rnb_engine_adam_guarded). */
+ * block (step count of applied steps as in rnb_engine_adam_guarded; [5] internal ticket, [6] != 0: a barrier spin timed out).
+ * flag_peers (HOST array of `world` device pointers, or NULL): every rank's RNB_PEER_FLAG_WORDS int32 barrier words, peer-
+ * mapped and zero at start.  Given, the ranks are ordered by FLAG BARRIERS over peer memory instead of collectives around the
+ * call: a one-warp kernel announces "backward of step barrier_value done" into every rank's words, the optimizer kernel
+ * spins (bounded) until every rank has announced before it reads a peer's gradients, its last block announces "shard
+ * stored everywhere", and a one-warp kernel holds the stream until every rank has.  barrier_value must grow by one per call
+ * (counters are never reset).  NULL: the caller orders the ranks (one barrier in front, one behind). */
+#define RNB_PEER_FLAG_WORDS (2 * RNB_MAX_PEERS)
 int rnb_engine_adam_sharded_guarded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers,
                                     float* params_f32, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded,
                                     float* zero_grads, float lr, float beta1, float beta2, float eps, float grad_scale,
-                                    int32_t* status, rnb_stream_t stream);
+                                    int32_t* status, void* const* flag_peers, int32_t barrier_value, rnb_stream_t stream);
 
 /* ------------------------------------------------------------------------------------
  * (callers of the path) Training-batch assembly on the device: replaces BaseDataset.__getitem__'s pixel sampling

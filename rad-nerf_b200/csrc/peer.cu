@@ -23,7 +23,40 @@ namespace rnb {
 struct PeerPtrs {
   const float* grads[RNB_MAX_PEERS];
   __half* p16[RNB_MAX_PEERS];
+  int32_t* flags[RNB_MAX_PEERS];      // every rank's barrier words (RNB_PEER_FLAG_WORDS), or all NULL: the caller orders the ranks
 };
+
+// ---- flag barrier over peer memory ------------------------------------------------------------------------------------
+// Every rank owns 2 x RNB_MAX_PEERS counters in its own (peer-mapped) memory: ARRIVE[p] is written by rank p when its backward
+// of step v is complete, DONE[p] when its optimizer kernel of step v has stored its shard everywhere.  Counters only grow
+// (v = optimizer step), so nothing is ever reset.  A spin is bounded (~seconds): on a timeout status[6] is set and the kernel
+// goes on, so a lost peer shows up as a reported error instead of a hung GPU.
+constexpr int kFlagArrive = 0, kFlagDone = RNB_MAX_PEERS;
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+  int32_t v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ bool spin_until(const int32_t* flag, int32_t value) {
+  for (int it = 0; it < (1 << 24); it++) {
+    if (ld_acquire_sys(flag) >= value) return true;
+    __nanosleep(it < 64 ? 20 : 200);
+  }
+  return false;
+}
+// one thread per peer: "my backward of step `value` is done" into every rank's ARRIVE[rank]
+__global__ void peer_signal_kernel(PeerPtrs P, int world, int rank, int slot, int32_t value) {
+  const int p = threadIdx.x;
+  if (p < world) { __threadfence_system(); st_release_sys(P.flags[p] + slot + rank, value); }
+}
+// one thread per peer: wait until every rank's counter in MY words has reached `value`
+__global__ void peer_wait_kernel(const int32_t* mine, int world, int slot, int32_t value, int32_t* status) {
+  const int p = threadIdx.x;
+  if (p < world && !spin_until(mine + slot + p, value) && status != nullptr) status[6] = 1;
+}
 
 // The W gradient vectors of one float4 index: every load is issued before any is used (the remote ones cross NVLink).
 template <int W>
@@ -75,11 +108,16 @@ __global__ void __launch_bounds__(256) adam_sharded_kernel(PeerPtrs P, int world
                                                            float* __restrict__ v, int64_t lo4, int64_t hi4, int64_t rep_lo4, int64_t rep_hi4,
                                                            float* __restrict__ zero_buf, int64_t zero_n4, float lr, int64_t host_step,
                                                            float beta1, float beta2, float eps, float grad_scale, int64_t flag_index,
-                                                           int32_t* __restrict__ status) {
+                                                           int32_t* __restrict__ status, int32_t barrier_value) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   float4 g[W];
   int64_t i = lo4 + t0;
+  // in-kernel barrier (flag words given): nothing of a peer is read before its ARRIVE counter shows this step
+  if (P.flags[rank] != nullptr) {
+    if (threadIdx.x < world && !spin_until(P.flags[rank] + kFlagArrive + threadIdx.x, barrier_value) && status != nullptr) status[6] = 1;
+    __syncthreads();
+  }
   if (i < hi4) load_peers<W>(P, world, i, g);
   // step guard: OR of every rank's flag word (peer loads) -> all ranks skip or apply the same step
   int flag_bits = 0;
@@ -95,7 +133,21 @@ __global__ void __launch_bounds__(256) adam_sharded_kernel(PeerPtrs P, int world
     for (int64_t z = t0; z < zero_n4; z += stride) __stcs(reinterpret_cast<float4*>(zero_buf) + z, make_float4(0.f, 0.f, 0.f, 0.f));
   // skipped step: nothing is applied.  The gradient buffer the peers are reading now is cleared by the NEXT step's kernel
   // like any other (zero_buf alternation), so there is nothing else to do.
-  if (sh.skip) return;
+  // "my optimizer kernel of this step is done" into every rank's DONE[rank], by the last block to get here: every block
+  // fences its peer stores first, so a rank that sees the counter also sees the parameters
+  auto signal_done = [&]() {
+    if (P.flags[rank] == nullptr) return;
+    __threadfence_system();
+    __syncthreads();
+    __shared__ int last;
+    if (threadIdx.x == 0) last = atomicAdd(status + 5, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (last) {
+      if (threadIdx.x == 0) status[5] = 0;
+      if (threadIdx.x < world) st_release_sys(P.flags[threadIdx.x] + kFlagDone + rank, barrier_value);
+    }
+  };
+  if (sh.skip) { signal_done(); return; }
   for (; i < hi4; i += stride) {
     float4 gn[W];
     const bool more = i + stride < hi4;
@@ -115,6 +167,7 @@ __global__ void __launch_bounds__(256) adam_sharded_kernel(PeerPtrs P, int world
     const float4 pp = adam4(add_peers<W>(world, g), p32, m, v, r, step_size, beta1, beta2, eps, inv_sqrt_bc2, grad_scale);
     reinterpret_cast<uint2*>(P.p16[rank])[r] = to_half4(pp);
   }
+  signal_done();
 }
 
 }  // namespace rnb
@@ -170,16 +223,17 @@ int rnb_adam_shard_bounds(int64_t n, int rank, int world, int64_t* lo, int64_t* 
 static int launch_adam_sharded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers, float* params_f32,
                                float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded, float* zero_grads, float lr, float beta1,
                                float beta2, float eps, int64_t step, float grad_scale, int64_t flag_index, int32_t* status,
-                               rnb_stream_t stream, const char* what) {
+                               void* const* flag_peers, int32_t barrier_value, rnb_stream_t stream, const char* what) {
   RNB_REQUIRE(world >= 1 && world <= RNB_MAX_PEERS && rank >= 0 && rank < world && grads_peers && params_f16_peers, what);
   RNB_REQUIRE(params_f32 && exp_avg && exp_avg_sq && n > 0 && n % 4 == 0 && step >= 1, what);
   RNB_REQUIRE(n_sharded > 0 && n_sharded <= n && n_sharded % 4 == 0 && ((uintptr_t)zero_grads & 15) == 0, what);
   PeerPtrs P;
-  for (int p = 0; p < RNB_MAX_PEERS; p++) { P.grads[p] = nullptr; P.p16[p] = nullptr; }
+  for (int p = 0; p < RNB_MAX_PEERS; p++) { P.grads[p] = nullptr; P.p16[p] = nullptr; P.flags[p] = nullptr; }
   for (int p = 0; p < world; p++) {
     RNB_REQUIRE(grads_peers[p] && params_f16_peers[p], what);
     RNB_REQUIRE(((uintptr_t)grads_peers[p] & 15) == 0 && ((uintptr_t)params_f16_peers[p] & 7) == 0, what);
     P.grads[p] = grads_peers[p]; P.p16[p] = (__half*)params_f16_peers[p];
+    if (flag_peers != nullptr) { RNB_REQUIRE(flag_peers[p] != nullptr && status != nullptr && barrier_value >= 1, what); P.flags[p] = (int32_t*)flag_peers[p]; }
   }
   int64_t lo, hi;
   if (int rc = rnb_adam_shard_bounds(n_sharded, rank, world, &lo, &hi)) return rc;
@@ -196,14 +250,18 @@ static int launch_adam_sharded(int rank, int world, const float* const* grads_pe
   int64_t blocks = ((zero_grads ? n : hi - lo) / 4 + 255) / 256;
   if (blocks > (int64_t)kNumSMs * per_sm) blocks = (int64_t)kNumSMs * per_sm;
   if (blocks < 1) blocks = 1;
+  // flag barrier: announce this rank's backward, let the kernel wait for everybody's, and hold the stream behind it until
+  // every rank's kernel has stored its shard here (three launches, no collective)
+  if (flag_peers != nullptr) peer_signal_kernel<<<1, 32, 0, as_stream(stream)>>>(P, world, rank, kFlagArrive, barrier_value);
 #define RNB_LAUNCH_ADAM_SHARDED(W)                                                                                                   \
   adam_sharded_kernel<W><<<(int)blocks, 256, 0, as_stream(stream)>>>(P, world, rank, params_f32, exp_avg, exp_avg_sq, lo / 4, hi / 4,   \
                                                                     n_sharded / 4, n / 4, zero_grads, n / 4, lr, step, beta1, beta2,    \
-                                                                    eps, grad_scale, flag_index, status)
+                                                                    eps, grad_scale, flag_index, status, barrier_value)
   if (width == 2) RNB_LAUNCH_ADAM_SHARDED(2);
   else if (width == 4) RNB_LAUNCH_ADAM_SHARDED(4);
   else RNB_LAUNCH_ADAM_SHARDED(RNB_MAX_PEERS);
 #undef RNB_LAUNCH_ADAM_SHARDED
+  if (flag_peers != nullptr) peer_wait_kernel<<<1, 32, 0, as_stream(stream)>>>(P.flags[rank], world, kFlagDone, barrier_value, status);
   return check_launch(what);
 }
 
@@ -211,17 +269,17 @@ int rnb_engine_adam_sharded(int rank, int world, const float* const* grads_peers
                             float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded, float* zero_grads, float lr, float beta1,
                             float beta2, float eps, int64_t step, float grad_scale, rnb_stream_t stream) {
   return launch_adam_sharded(rank, world, grads_peers, params_f16_peers, params_f32, exp_avg, exp_avg_sq, n, n_sharded, zero_grads, lr,
-                             beta1, beta2, eps, step, grad_scale, -1, nullptr, stream, "rnb_engine_adam_sharded");
+                             beta1, beta2, eps, step, grad_scale, -1, nullptr, nullptr, 0, stream, "rnb_engine_adam_sharded");
 }
 
 int rnb_engine_adam_sharded_guarded(int rank, int world, const float* const* grads_peers, void* const* params_f16_peers,
                                     float* params_f32, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t n_sharded,
                                     float* zero_grads, float lr, float beta1, float beta2, float eps, float grad_scale,
-                                    int32_t* status, rnb_stream_t stream) {
+                                    int32_t* status, void* const* flag_peers, int32_t barrier_value, rnb_stream_t stream) {
   const char* what = "rnb_engine_adam_sharded_guarded";
   RNB_REQUIRE(status != nullptr, what);
   return launch_adam_sharded(rank, world, grads_peers, params_f16_peers, params_f32, exp_avg, exp_avg_sq, n, n_sharded, zero_grads, lr,
-                             beta1, beta2, eps, 1, grad_scale, n, status, stream, what);
+                             beta1, beta2, eps, 1, grad_scale, n, status, flag_peers, barrier_value, stream, what);
 }
 
 }  // extern "C"

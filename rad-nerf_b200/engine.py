@@ -122,6 +122,8 @@ class Engine:
             self._peer_g = [parallel.PeerBuffer((off + GRAD_TAIL) * 4, dev), parallel.PeerBuffer((off + GRAD_TAIL) * 4, dev)]
             self._peer_p = parallel.PeerBuffer(off * 2, dev)
             self._g = 0
+            # barrier words of the flag barrier (csrc/peer.cu): words 16.. of buffer 0's tail on every rank, as mapped here
+            self._flag_ptrs = (ctypes.c_void_p * self.world)(*[p + (off + 16) * 4 for p in self._peer_g[0].ptrs])
             self._grad_buf = self._peer_g[0].local.view(torch.float32)
             self.flat16 = self._peer_p.local.view(torch.float16)
         else:
@@ -352,16 +354,19 @@ class Engine:
             # cleared.  The stream barrier in front orders it after every rank's backward (and gradient check).  Behind it a
             # second barrier keeps every rank's next step (field kernels, occupancy update, rendering: all readers of the
             # fp16 parameters) behind every peer's parameter stores.
-            sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             cur, prev = self._peer_g[self._g], self._peer_g[self._g ^ 1]
             n_sharded = self.offsets["gate"] if self.K > 1 else self.n_params
+            flag_barrier = os.environ.get("RNB_NCCL_BARRIER", "0") != "1"
+            if not flag_barrier:      # A/B: order the ranks with two 4-byte NCCL all-reduces instead of the flag barrier
+                sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             sp = _Span(_Span.ADAM, self.device)
             call("rnb_engine_adam_sharded_guarded", i32(parallel.rank()), i32(self.world), cur.pointer_array(),
                  self._peer_p.pointer_array(), self.flat, self.exp_avg, self.exp_avg_sq, i64(self.n_params), i64(n_sharded),
                  prev.local, f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps),
-                 f32(1.0), self.status, stream_arg(self.device))
+                 f32(1.0), self.status, self._flag_ptrs if flag_barrier else None, i32(self.opt_step), stream_arg(self.device))
             sp.end()
-            sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
+            if not flag_barrier:
+                sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
             self._g ^= 1
             self._grad_buf = self._peer_g[self._g].local.view(torch.float32)      # (cleared by the kernel of the previous step)
             self.grads = self._grad_buf[:n]
