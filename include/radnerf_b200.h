@@ -99,6 +99,25 @@ int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, float 
                                 int64_t cap, float* xyzs, float* dirs, float* deltas, float* ts,
                                 rnb_stream_t stream);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  rnb_raymarching_train_count +
+ * rnb_raymarching_train_write in ONE call that allocates nothing: the per-ray sample-t scratch (t_scratch above) is a
+ * file-scope device array inside the library of RNB_NOALLOC_MARCH_MAX_FLOATS floats (32 MiB, held by every GPU that loads
+ * the library until exit); n_rays * max_samples beyond that is rejected with RNB_ERR_BADARG and a message.  The caller
+ * passes inputs and ALL outputs: rays_a (n_rays,3) i64, counter (2) i32, and xyzs / dirs (cap,3), deltas / ts (cap) f32 --
+ * samples whose slot is >= cap are dropped (counter[0] holds the true total, so the caller can tell).  Same kernels, so the
+ * results are bit-identical to the two-phase pair.  No host synchronisation, no cudaMalloc / cudaFree / allocating
+ * library call; the first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device).
+ * Every call on a device SHARES the one array: calls that overlap on the GPU (different streams, or concurrent graph
+ * launches) race -- serialise them.  The array keeps the last call's contents; nothing in it needs to start at zero
+ * (only entries written by this call are read). */
+#define RNB_NOALLOC_MARCH_MAX_FLOATS (8 * 1024 * 1024)
+int rnb_raymarching_train_noalloc(const float* rays_o, const float* rays_d, const float* hits_t,
+                                  const uint8_t* density_bitfield, int cascades, float scale,
+                                  float exp_step_factor, const float* noise, int grid_size, int max_samples,
+                                  int64_t n_rays, int64_t* rays_a, int32_t* counter, int64_t cap, float* xyzs,
+                                  float* dirs, float* deltas, float* ts, rnb_stream_t stream);
+
 /* binding.cpp:84-106 -> raymarching.cu:335-454.  hits_t (n_rays_total,2) f32 is MUTATED
  * ([r][0] <- resume point).  alive_indices (n_alive) i64.  Outputs (n_alive,N_samples[,3])
  * f32 are fully written (unused slots = 0, like the reference's zero-filled slabs) and

@@ -173,6 +173,74 @@ int rnb_raymarching_train_write(const float* rays_o, const float* rays_d, float 
   return check_launch(what);
 }
 
+// ---- no-allocation variant of the training marcher ----------------------------------------------------------------
+// (No counterpart in the reference: added for callers that cannot call cudaMalloc --
+// code under CUDA-graph capture, tight serving loops, harnesses that forbid it.)  Same kernels as
+// rnb_raymarching_train_count + rnb_raymarching_train_write; the per-ray sample-t rows live in g_noalloc_t_scratch below
+// instead of a caller buffer.  The array is file-scope device memory: every GPU that loads the library holds its 32 MiB
+// until exit.  In HOST code the array's name is only a stand-in for the symbol, not a device address: its address is taken
+// once per device, with that device current, through cudaGetSymbolAddress, and that pointer is what the kernels get.
+}  // extern "C"
+namespace rnb {
+static __device__ __align__(256) float g_noalloc_t_scratch[RNB_NOALLOC_MARCH_MAX_FLOATS];
+}
+#include <mutex>
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_noalloc_ptr[kMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+// the device address of the scratch array on the CURRENT device (set-up on the first call per device)
+int noalloc_scratch(float** out, const char* what) {
+  int dev = -1;
+  RNB_CUDA(cudaGetDevice(&dev), what);
+  RNB_REQUIRE(dev >= 0 && dev < kMaxDevices, what);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    RNB_CUDA(cudaGetSymbolAddress((void**)&p, rnb::g_noalloc_t_scratch), what);
+    RNB_REQUIRE(p != nullptr, what);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return RNB_OK;
+}
+}  // namespace
+extern "C" {
+
+int rnb_raymarching_train_noalloc(const float* rays_o, const float* rays_d, const float* hits_t, const uint8_t* density_bitfield,
+                                  int cascades, float scale, float exp_step_factor, const float* noise, int grid_size,
+                                  int max_samples, int64_t n_rays, int64_t* rays_a, int32_t* counter, int64_t cap, float* xyzs,
+                                  float* dirs, float* deltas, float* ts, rnb_stream_t stream) {
+  const char* what = "rnb_raymarching_train_noalloc";
+  RNB_REQUIRE(n_rays >= 0 && cap >= 0 && cascades >= 1 && grid_size >= 1 && grid_size <= 1024 && max_samples >= 1, what);
+  RNB_REQUIRE(counter != nullptr, what);
+  if (n_rays * (int64_t)max_samples > (int64_t)RNB_NOALLOC_MARCH_MAX_FLOATS) {
+    set_error("%s: n_rays * max_samples = %lld exceeds the built-in scratch of %lld floats (RNB_NOALLOC_MARCH_MAX_FLOATS); "
+              "use rnb_raymarching_train_count / _write with a caller-provided t_scratch",
+              what, (long long)(n_rays * (int64_t)max_samples), (long long)RNB_NOALLOC_MARCH_MAX_FLOATS);
+    return RNB_ERR_BADARG;
+  }
+  RNB_REQUIRE(n_rays == 0 || (rays_o && rays_d && hits_t && density_bitfield && noise && rays_a), what);
+  RNB_REQUIRE(n_rays == 0 || cap == 0 || (xyzs && dirs && deltas && ts), what);
+  float* t_scratch = nullptr;
+  if (int rc = noalloc_scratch(&t_scratch, what)) return rc;
+  cudaStream_t st = as_stream(stream);
+  const MarchParams p = make_march_params(density_bitfield, cascades, scale, exp_step_factor, grid_size, max_samples, scale);
+  // nothing of the scratch has to start at zero: a row's first N_samples entries are written by the count kernel and
+  // only those are read by the write kernel, so the previous call's contents are never seen
+  if (n_rays > 0) {
+    const int grid = ceil_div(n_rays * 32, 256);
+    if (exp_step_factor == 0.0f)
+      march_train_count_kernel<true><<<grid, 256, 0, st>>>(rays_o, rays_d, hits_t, noise, p, n_rays, rays_a, t_scratch);
+    else
+      march_train_count_kernel<false><<<grid, 256, 0, st>>>(rays_o, rays_d, hits_t, noise, p, n_rays, rays_a, t_scratch);
+  }
+  march_train_scan_kernel<<<1, 1024, 0, st>>>(n_rays, rays_a, counter);
+  if (n_rays > 0 && cap > 0)
+    march_train_write_kernel<<<ceil_div(n_rays * 32, 256), 256, 0, st>>>(rays_o, rays_d, p, n_rays, rays_a, t_scratch, cap, xyzs, dirs, deltas, ts);
+  return check_launch(what);
+}
+
 int rnb_raymarching_test(const float* rays_o, const float* rays_d, float* hits_t, const int64_t* alive_indices,
                          int64_t n_alive, const uint8_t* density_bitfield, int cascades, float scale,
                          float exp_step_factor, int grid_size, int max_samples, int N_samples, float* xyzs,
