@@ -271,10 +271,14 @@ def run_product(args):
     from radnerf_b200.trainer import Trainer
     lib = _lib.lib()   # fail loudly if the CUDA library is missing: there is no fallback
     K = w["K"]
+    # --graph (single process): the step is replayed from captured CUDA graphs (Trainer(graph=True))
+    # (default: eager launches -- the host enqueues a step in 0.29 ms against 0.62 ms on the device, so the device never waits,
+    # and a graph launch adds ~0.01 ms at every step boundary; --graph: replay, host 0.12 ms/step)
+    use_graph = world == 1 and args.graph and not args.python_surface and not args.no_march_ahead
     # weak scaling (default): 8192 rays per GPU; strong: a global batch of 8192 rays split over the ranks
     batch = BATCH // world if args.scaling == "strong" else BATCH
     tr = Trainer(scale=w["scale"], K=K, freeze_occupancy=True, device=f"cuda:{local}", engine=not args.python_surface,
-                 batch_rays=batch)
+                 batch_rays=batch, graph=use_graph)
     tr.set_occupancy(scene_bitfields(syn, w))
     host = [tuple(torch.from_numpy(a).pin_memory() for a in b) for b in make_batches(syn, w, rank, batch=batch)]
     dev = [tuple(a.cuda(non_blocking=True) for a in b) for b in host]
@@ -312,7 +316,7 @@ def run_product(args):
     def dev_step(s):
         flush_l2()
         nxt = dev[(s + 1) % len(dev)]
-        tr.step(*dev[s % len(dev)], next_rays=nxt[:2] if ahead else None)
+        tr.step(*dev[s % len(dev)], next_rays=(nxt if use_graph else nxt[:2]) if ahead else None)
 
     def plain_step(s):      # no marching ahead: clean per-stage times for the roofline leg
         flush.add_(1.0)
@@ -369,7 +373,7 @@ def run_product(args):
                 tr.step(o, d, t)
             else:
                 nxt = feeder.peek(s + 1)
-                tr.step(o, d, t, next_rays=nxt[:2])
+                tr.step(o, d, t, next_rays=nxt if use_graph else nxt[:2])
             feeder.done(s)
         read_back(s, tr.engine.loss if tr.engine is not None else tr.last_loss.reshape(1).expand(8))
 
@@ -391,7 +395,7 @@ def run_product(args):
     # the same loop without the L2 flush (nothing subtracted): parameters and inputs of the previous step stay in L2
     def noflush_step(s):
         nxt = dev[(s + 1) % len(dev)]
-        tr.step(*dev[s % len(dev)], next_rays=nxt[:2] if ahead else None)
+        tr.step(*dev[s % len(dev)], next_rays=(nxt if use_graph else nxt[:2]) if ahead else None)
     noflush_step(0)
     ms_noflush = timed(lambda s: noflush_step(s + 1), args.steps) / args.steps
     for s in range(args.warmup):         # untimed: feeder slots, copy / read-back streams and pinned buffers come up here
@@ -401,6 +405,7 @@ def run_product(args):
     stage_ms = {}
     if tr.engine is not None:
         tr.engine._ahead.clear()
+        tr.stepper, tr._staged = None, None      # the per-stage events are recorded by the library's host code: eager launches here
         torch.cuda.synchronize()
         lib.rnb_engine_profile(1)
         timed(plain_step, args.steps)
@@ -437,7 +442,7 @@ def run_product(args):
             "config": arm_config(args, w, world),
             "run": {"batch_rays_this_rank": batch,
                     "occupancy_update": "every 16 steps, on shadow grids (the marched occupancy stays the analytic scene's)",
-                    "march_ahead": bool(ahead),
+                    "march_ahead": bool(ahead), "cuda_graph": bool(use_graph),
                     "path": "fused engine (rnb_engine_*)" if tr.engine is not None else "python operator surface"},
             "ms_per_step_noflush": ms_noflush, "value_noflush": rays_total / (ms_noflush * 1e-3),
             "clocks": clk,
@@ -608,6 +613,7 @@ def main():
     ap.add_argument("--workload", default="radnerf_tat_k2")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: 8192 rays per GPU (default); strong: a global batch of 8192 rays split over the ranks")
+    ap.add_argument("--graph", action="store_true", help="replay the step from captured CUDA graphs (single process) instead of eager launches")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-march-ahead", action="store_true", help="march every batch inside its own step (single stream)")
     ap.add_argument("--python-surface", action="store_true", help="time the drop-in Python operator surface instead of the fused engine")

@@ -320,6 +320,7 @@ typedef struct {
   int64_t geo_off[RNB_MAX_K];
   int64_t rgb_off[RNB_MAX_K];
   int64_t gate_off;              /* ignored when K == 1                                                      */
+  uint64_t noise_seed;           /* seed of the library's own marching noise (used when the caller passes noise = NULL) */
 } rnb_engine_config;
 
 /* byte offsets into the caller's workspace (all 256-byte aligned) */
@@ -342,10 +343,13 @@ typedef struct {
   int64_t march_slot_bytes;
   int64_t coarse;                /* u64 (K,4096): dilated 64^3-block occupancy (bit x of word y + 64 z), part of the march slot; used
                                   * for the marcher's empty-space test when cascades == 1 and grid_size == 128     */
-  int64_t status;                /* i32 (8) step guard (GradScaler equivalent, see rnb_engine_adam_guarded): [0] optimizer steps skipped
+  int64_t status;                /* i32 (16) step guard (GradScaler equivalent, see rnb_engine_adam_guarded): [0] optimizer steps skipped
                                   * for a non-finite / saturated gradient, [1] steps skipped because the samples exceeded
                                   * sample_capacity, [2] largest (128-aligned) sample count any step needed, [3] optimizer steps
-                                  * applied, [4] internal ticket.  The caller zeroes it once; the library only counts up. */
+                                  * applied, [4]-[5] internal tickets, [6] != 0: a peer barrier timed out, [7] / [9] marching
+                                  * calls so far into slot 0 / 1 (the library's noise streams), [8] learning rate as float bits, read by the optimizer
+                                  * kernels when they are called with lr < 0 (a captured CUDA graph can then be replayed under a
+                                  * schedule: the host writes the value before the replay).  16 words.  The caller zeroes it once. */
 } rnb_engine_layout;
 
 /* Step guard.  The reference trains with Lightning precision=16 (train_ml.py:304): a dynamic GradScaler that skips the
@@ -368,7 +372,8 @@ int rnb_engine_gate(const rnb_engine_config* cfg, void* workspace, const void* p
 /* Phase 2: march, field, composite, blend, loss, and the complete backward.  `importance` (K) f32 device:
  * the GLOBAL importance (all-reduced over ranks when data parallel; the workspace's own buffer otherwise).
  * n_rays_global: rays of the whole (multi-rank) batch, the denominator of the loss means.
- * bitfields: HOST array of K device pointers; noise (K,n_rays) f32 device in [0,1); bg (K,3) f32 HOST
+ * bitfields: HOST array of K device pointers; noise (K,n_rays) f32 device in [0,1), or NULL: the library draws it from its own
+ * counter generator (cfg->noise_seed, one stream of draws per marching call: no launch outside the library); bg (K,3) f32 HOST
  * (background colour per pass, Q17).  Gradients are ACCUMULATED into grads_f32 (flat, fp32; n_params + RNB_GRAD_TAIL floats:
  * the flag word of the step guard sits at index n_params and is cleared at the start of a step with_backward). */
 int rnb_engine_fwd_bwd(const rnb_engine_config* cfg, void* workspace, const void* params_f16, float* grads_f32,

@@ -14,6 +14,7 @@ __device__ __forceinline__ void adam_prologue(AdamStep* sh, int flag_bits, int32
                                               float beta2) {
   if (threadIdx.x == 0) {
     const int64_t step = status != nullptr ? (int64_t)*(volatile int32_t*)(status + 3) + 1 : host_step;
+    if (lr < 0.f && status != nullptr) lr = __int_as_float(*(volatile int32_t*)(status + 8));   // schedule value written by the host (graph replay)
     const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
     sh->step_size = (float)((double)lr / bc1); sh->inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2)); sh->skip = flag_bits;
     if (status != nullptr) {

@@ -72,6 +72,16 @@ __device__ __forceinline__ void st_stream_f32x4(float4* p, float4 v) {
                "f"(v.z), "f"(v.w));
 }
 
+// uniform [0,1) from a 64-bit counter (splitmix64 finaliser; 24 mantissa bits): the library's own generator where the caller
+// supplies no random inputs (marching noise) -- no ATen launch inside the step, so the step can be captured in a CUDA graph
+__device__ __forceinline__ float counter_uniform(uint64_t seed, uint64_t ctr) {
+  uint64_t z = seed + (ctr + 1) * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(uint32_t)(z >> 40) * (1.0f / 16777216.0f);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);

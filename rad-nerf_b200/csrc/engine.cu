@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
                                                         const float* __restrict__ noise, MarchParams p, BitfieldPtrs bf,
                                                         float cx, float cy, float cz, float hx, float hy, float hz, float near_d,
                                                         int n_rays, int32_t* __restrict__ counts, float* __restrict__ t_scratch,
-                                                        const uint64_t* __restrict__ coarse) {
+                                                        const uint64_t* __restrict__ coarse, uint64_t noise_seed,
+                                                        const int32_t* __restrict__ march_calls, uint64_t noise_slot_salt) {
   const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int pass = blockIdx.y;
   if (r >= n_rays) return;
@@ -98,7 +99,13 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
   // empty-space test against the dilated coarse grid (coarse.cuh): skip rays that cannot meet an occupied cell, stop the
   // others behind the last block they can meet
   if (coarse != nullptr && t1 >= 0 && t1 < t2) t2 = coarse_last_hit(ray, t1, t2, coarse + (int64_t)pass * p.cascades * kCoarseWords, p.cascades, p.scale);
-  if (t1 >= 0) t1 = __fmaf_rn(calc_dt(t1, p), __ldg(noise + (int64_t)pass * n_rays + r), t1);
+  // perturbation (raymarching.cu:195-198): the caller's noise, or -- none given -- the library's counter generator keyed by
+  // (seed, march call, pass, ray): one fresh draw per sub-NeRF call like the reference's rand_like (custom_functions.py:83)
+  if (t1 >= 0) {
+    const float u = noise != nullptr ? __ldg(noise + (int64_t)pass * n_rays + r)
+                                     : counter_uniform(noise_seed, ((uint64_t)(uint32_t)*march_calls * gridDim.y + pass) * (uint64_t)n_rays + r + noise_slot_salt);
+    t1 = __fmaf_rn(calc_dt(t1, p), u, t1);
+  }
   float t_next;
   const int64_t row = (int64_t)pass * n_rays + r;
   const int n = t2 < 0 ? 0 : march_ray_warp<kConstDt, kOneCascade>(ray, p, bf.p[pass], t1, t2, p.max_samples, t_scratch + row * p.max_samples, t_next);
@@ -109,7 +116,7 @@ __global__ void __launch_bounds__(256) eng_march_kernel(const float* __restrict_
 // so that a 128-sample tile never straddles two passes.  seg = [base_0..base_{K-1}, end, n_0..n_{K-1},
 // overflow, total].
 __global__ void __launch_bounds__(1024) eng_scan_kernel(const int32_t* __restrict__ counts, int n_rays, int K, int64_t capacity,
-                                                        int32_t* __restrict__ starts, int32_t* __restrict__ seg) {
+                                                        int32_t* __restrict__ starts, int32_t* __restrict__ seg, int32_t* __restrict__ march_calls) {
   __shared__ int warp_tot[32];
   __shared__ int carry_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -154,6 +161,7 @@ __global__ void __launch_bounds__(1024) eng_scan_kernel(const int32_t* __restric
     seg[K] = base;
     seg[2 * K + 1] = (int64_t)base > capacity ? 1 : 0;
     seg[2 * K + 2] = total;
+    *march_calls += 1;          // the marching kernel in front of this one has drawn its noise: next call, next stream of draws
   }
 }
 
@@ -467,7 +475,7 @@ int rnb_engine_layout_of(const rnb_engine_config* c, rnb_engine_layout* L) {
   L->d_pass_opacity = w.take(K * R * 4); L->d_pass_depth = w.take(K * R * 4); L->d_pass_rgb = w.take(K * R * 3 * 4);
   L->rgb = w.take(R * 3 * 4); L->opacity = w.take(R * 4); L->depth = w.take(R * K * 4);
   L->loss = w.take(8 * 4);
-  L->status = w.take(8 * 4);
+  L->status = w.take(16 * 4);
   L->march_slot_bytes = L->enc - L->t_scratch;     // [t_scratch, counts, starts, seg, ray_id, ts, deltas] are contiguous
   L->march_slot1 = w.take(L->march_slot_bytes);
   L->total_bytes = w.off;
@@ -507,7 +515,7 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
                      const uint8_t* const* bitfields, int slot, rnb_stream_t stream) {
   const char* what = "rnb_engine_march";
   if (int rc = check_cfg(c, what)) return rc;
-  RNB_REQUIRE(workspace && rays_o && rays_d && noise && bitfields && (slot == 0 || slot == 1), what);
+  RNB_REQUIRE(workspace && rays_o && rays_d && bitfields && (slot == 0 || slot == 1), what);
   rnb_engine_layout L;
   rnb_engine_layout_of(c, &L);
   char* ws = (char*)workspace + (slot == 1 ? L.march_slot1 - L.t_scratch : 0);
@@ -517,6 +525,9 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
   int32_t* counts = (int32_t*)(ws + L.counts); int32_t* starts = (int32_t*)(ws + L.starts); int32_t* seg = (int32_t*)(ws + L.seg);
   float* t_scratch = (float*)(ws + L.t_scratch);
   int32_t* ray_id = (int32_t*)(ws + L.ray_id); float* ts = (float*)(ws + L.ts); float* deltas = (float*)(ws + L.deltas);
+  // calls so far INTO THIS SLOT (status[7] / status[9]): the two slots are marched on different streams, possibly at the same
+  // time, so each keeps its own count; (slot, count, pass, ray) keys the noise draw
+  int32_t* march_calls = (int32_t*)((char*)workspace + L.status) + (slot == 0 ? 7 : 9);
   const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, c->scale);
   BitfieldPtrs bf;
   for (int i = 0; i < K; i++) { RNB_REQUIRE(bitfields[i] != nullptr, what); bf.p[i] = bitfields[i]; }
@@ -532,13 +543,13 @@ int rnb_engine_march(const rnb_engine_config* c, void* workspace, const float* r
 #define RNB_ENG_MARCH(CONST_DT, ONE)                                                                                              \
   eng_march_kernel<CONST_DT, ONE><<<ray_grid, 256, 0, st>>>(rays_o, rays_d, noise, mp, bf, c->center[0], c->center[1], c->center[2], \
                                                             c->half_size[0], c->half_size[1], c->half_size[2], c->near_distance, R,  \
-                                                            counts, t_scratch, coarse)
+                                                            counts, t_scratch, coarse, c->noise_seed, march_calls, slot ? (1ull << 62) : 0ull)
   if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_ENG_MARCH(true, true);     // bounded scenes (train_ml.py:99-101)
   else if (c->exp_step_factor == 0.0f) RNB_ENG_MARCH(true, false);
   else RNB_ENG_MARCH(false, false);
 #undef RNB_ENG_MARCH
   }
-  { StageTimer tm(ST_SCAN, st); eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg); }
+  { StageTimer tm(ST_SCAN, st); eng_scan_kernel<<<1, 1024, 0, st>>>(counts, R, K, S, starts, seg, march_calls); }
   { StageTimer tm(ST_EXPAND, st); eng_expand_kernel<<<ray_grid, 256, 0, st>>>(counts, starts, t_scratch, mp, R, S, ray_id, ts, deltas); }
   return check_launch(what);
 }
@@ -589,7 +600,7 @@ int rnb_engine_fwd_bwd_ex(const rnb_engine_config* c, void* workspace, const voi
   const MarchParams mp = make_march_params(nullptr, c->cascades, c->scale, c->exp_step_factor, c->grid_size, c->max_samples, c->scale);
   const dim3 ray_grid(ceil_div((int64_t)R * 32, 256), K);
   if (march_slot < 0) {
-    RNB_REQUIRE(noise && bitfields, what);
+    RNB_REQUIRE(bitfields, what);
     if (int rc = rnb_engine_march(c, workspace, rays_o, rays_d, noise, bitfields, 0, stream)) return rc;
   }
   // 4. field forward

@@ -33,7 +33,8 @@ class _Config(ctypes.Structure):
                 ("lambda_opacity", ctypes.c_float), ("lambda_cv", ctypes.c_float), ("lambda_dm", ctypes.c_float),
                 ("loss_scale", ctypes.c_float),
                 ("n_params", ctypes.c_int64), ("table_off", ctypes.c_int64),
-                ("geo_off", ctypes.c_int64 * MAX_K), ("rgb_off", ctypes.c_int64 * MAX_K), ("gate_off", ctypes.c_int64)]
+                ("geo_off", ctypes.c_int64 * MAX_K), ("rgb_off", ctypes.c_int64 * MAX_K), ("gate_off", ctypes.c_int64),
+                ("noise_seed", ctypes.c_uint64)]
 
 
 _LAYOUT_FIELDS = ["total_bytes", "gate_in", "gate_hidden", "gate_logits", "gate_dlogits", "gate_prob", "dgate", "importance",
@@ -157,6 +158,7 @@ class Engine:
         for i in range(K):
             c.geo_off[i], c.rgb_off[i] = offs[f"geo{i}"], offs[f"rgb{i}"]
         c.gate_off = offs.get("gate", 0)
+        c.noise_seed = 0x5EED5EED + 7919 * parallel.rank()
         self.cfg = c
         self.samples_per_ray = int(samples_per_ray)
         self.on_overflow = on_overflow
@@ -195,7 +197,7 @@ class Engine:
         self.pass_depth = v("pass_depth", torch.float32, (K, R)); self.pass_total = v("pass_total", torch.int32, (K, R))
         self.rgb = v("rgb", torch.float32, (R, 3)); self.opacity = v("opacity", torch.float32, (R,)); self.depth = v("depth", torch.float32, (R, K))
         self.loss = v("loss", torch.float32, (8,))
-        self.status = v("status", torch.int32, (8,))
+        self.status = v("status", torch.int32, (16,))
         self.status.zero_()
         if any(self._status_seen):        # re-allocation (capacity growth): carry the counters over
             self.status[:4] = torch.tensor(self._status_seen, dtype=torch.int32, device=self.device)
@@ -229,7 +231,7 @@ class Engine:
         return self.ws[off:off + v.numel() * v.element_size()].view(dtype).view(*shape)
 
     # -- phases -------------------------------------------------------------------------------------------
-    def prefetch(self, rays_o, rays_d, noise=None):
+    def prefetch(self, rays_o, rays_d, noise=None, slot=None):
         """March the NEXT batch (AABB, march, scan, expand: everything that depends on rays and occupancy only) on a
         side stream while the kernels of the current step run.  Call it BEFORE step() of the current batch; the
         following step()/forward_backward() on these same tensors picks the samples up.  The bitfields must not
@@ -239,14 +241,14 @@ class Engine:
         assert rays_o.shape[0] == self.n_rays
         while len(self._ahead) > 1:             # never picked up: let it finish, then forget it
             torch.cuda.current_stream(self.device).wait_event(self._ahead.pop(next(iter(self._ahead)))[4])
-        if noise is None:
-            noise = torch.rand(self.K, self.n_rays, device=self.device)
+        if noise is not None:       # (None: the library draws the marching noise itself -- no ATen launch in the step)
+            _lib.check_input(noise, "noise", torch.float32)
         if self._march_stream is None:
             self._march_stream = torch.cuda.Stream(self.device)
         # the batch being (or about to be) trained sits in the slot of its own prefetch if that is still pending, else in
         # self._slot (forward_backward has already claimed it)
         busy = next(iter(self._ahead.values()))[0] if self._ahead else self._slot
-        slot = busy ^ 1
+        slot = (busy ^ 1) if slot is None else slot
         cur = torch.cuda.current_stream(self.device)
         ready = torch.cuda.Event()
         ready.record(cur)                       # inputs produced / the slot's previous reader (two steps back) finished
@@ -269,8 +271,9 @@ class Engine:
         for t, n in ((rays_o, "rays_o"), (rays_d, "rays_d"), (target_rgb, "target_rgb")):
             _lib.check_input(t, n, torch.float32)
         assert rays_o.shape[0] == self.n_rays
-        self.sync_params()      # cheap version check: fp32 parameters changed through torch (load_state_dict) -> fp16 copies
-        self._poll_guard()      # act on the status the device reported for earlier steps (loss scale, capacity)
+        if not torch.cuda.is_current_stream_capturing():
+            self.sync_params()      # cheap version check: fp32 parameters changed through torch (load_state_dict) -> fp16 copies
+            self._poll_guard()      # act on the status the device reported for earlier steps (loss scale, capacity)
         cur = torch.cuda.current_stream(self.device)
         hit = self._ahead.pop((rays_o.data_ptr(), rays_d.data_ptr()), None)
         if hit is not None:
@@ -284,10 +287,11 @@ class Engine:
             for k in keys[:-1]:
                 cur.wait_event(self._ahead.pop(k)[4])
             march_slot = (self._ahead[keys[-1]][0] ^ 1) if keys else 0
-            if noise is None:
-                noise = torch.rand(self.K, self.n_rays, device=self.device)
-            _lib.check_input(noise, "noise", torch.float32)
-            assert noise.numel() == self.K * self.n_rays
+            if getattr(self, "_force_slot", None) is not None:      # (graph replay: static batch slot == march slot)
+                march_slot = self._force_slot
+            if noise is not None:
+                _lib.check_input(noise, "noise", torch.float32)
+                assert noise.numel() == self.K * self.n_rays
         self._slot = march_slot
         inline = hit is None
         st = stream_arg(self.device)
@@ -338,7 +342,7 @@ class Engine:
                 joined = torch.cuda.Event(); joined.record(self._gate_stream)
             cur.wait_event(joined)            # whatever follows on the step's stream (the optimizer) sees the gate gradients
 
-    def adam_step(self, lr=None):
+    def adam_step(self, lr=None, lr_from_device=False):
         """Optimizer step behind the step guard: an inf / nan in the dense networks' gradients is looked for here
         (rnb_engine_grad_check; the table gradient and the fp16 seeds are checked where they are produced), then the
         Adam kernel applies the step -- or, when the flag word is set on ANY rank, clears the gradients and leaves
@@ -362,8 +366,8 @@ class Engine:
             sp = _Span(_Span.ADAM, self.device)
             call("rnb_engine_adam_sharded_guarded", i32(parallel.rank()), i32(self.world), cur.pointer_array(),
                  self._peer_p.pointer_array(), self.flat, self.exp_avg, self.exp_avg_sq, i64(self.n_params), i64(n_sharded),
-                 prev.local, f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps),
-                 f32(1.0), self.status, self._flag_ptrs if flag_barrier else None, i32(self.opt_step), stream_arg(self.device))
+                 prev.local, f32(-1.0 if lr_from_device else (self.lr if lr is None else lr)), f32(self.betas[0]), f32(self.betas[1]),
+                 f32(self.eps), f32(1.0), self.status, self._flag_ptrs if flag_barrier else None, i32(self.opt_step), stream_arg(self.device))
             sp.end()
             if not flag_barrier:
                 sp = _Span(_Span.BARRIER, self.device); parallel.stream_barrier(self.device); sp.end()
@@ -376,8 +380,8 @@ class Engine:
             if self.world > 1:                       # ... and every rank must take the same skip decision
                 dist.all_reduce(flags[:1].view(torch.int32), op=dist.ReduceOp.MAX)
             call("rnb_engine_adam_guarded", self.flat, self.flat16, self._grad_buf, self.exp_avg, self.exp_avg_sq, i64(n),
-                 f32(self.lr if lr is None else lr), f32(self.betas[0]), f32(self.betas[1]), f32(self.eps), f32(1.0),
-                 flags, self.status, stream_arg(self.device))
+                 f32(-1.0 if lr_from_device else (self.lr if lr is None else lr)), f32(self.betas[0]), f32(self.betas[1]),
+                 f32(self.eps), f32(1.0), flags, self.status, stream_arg(self.device))
         if self.opt_step % self.status_interval == 0:
             self._post_status()
 
@@ -385,8 +389,10 @@ class Engine:
     def _post_status(self):
         """Asynchronous read-back of the status counters into a pinned ring; consumed by _poll_guard one or more steps
         later (the host never waits for the device here)."""
+        if torch.cuda.is_current_stream_capturing():
+            return          # (inside a CUDA-graph capture: the read-back is issued by the replaying side)
         if self._status_ring is None:
-            self._status_ring = {"pin": torch.zeros(4, 8, dtype=torch.int32).pin_memory(), "evt": [None] * 4, "k": 0,
+            self._status_ring = {"pin": torch.zeros(4, 16, dtype=torch.int32).pin_memory(), "evt": [None] * 4, "k": 0,
                                  "stream": torch.cuda.Stream(self.device)}
         r = self._status_ring
         k = r["k"] % 4
@@ -482,6 +488,10 @@ class Engine:
         self.forward_backward(rays_o, rays_d, target_rgb, noise, self.background(random_bg), True, next_rays)
         self.adam_step(lr)
         return self.loss
+
+    def graph_stepper(self):
+        """CUDA-graph replay of the step (GraphStepper): single-process engines only."""
+        return GraphStepper(self)
 
     def results(self):
         """The reference's ml_render result dict (ml_rendering.py:72-77) as views of the workspace ("independent_rgbs",
@@ -600,3 +610,150 @@ class Engine:
         seg = self._slot_view("seg", torch.int32, (2 * MAX_K + 4,), self._slot).tolist()
         K = self.K
         return seg[K + 1:2 * K + 1], bool(seg[2 * K + 1])
+
+
+class GraphStepper:
+    """The training step as CUDA graphs ("CUDA-graph-captured step").
+
+    The eager step costs ~0.45 ms of host time (a dozen ctypes calls, stream and event bookkeeping) against ~0.63 ms on the
+    device; replaying a captured graph costs a few tens of microseconds.  What makes the step capturable: sample counts never
+    leave the device, the marching noise comes from the library's counter generator (no ATen launch), the count of applied
+    optimizer steps and the learning rate are read from device memory (status[3], status[8]), and the step guard skips a bad
+    step on the device.  Outside the graphs: the occupancy update (every 16 steps), the upload of the next batch, the
+    4-byte learning-rate write and the status read-back.
+
+    Two static batch slots alternate: the graph of slot s trains on the batch in slot s and (kind "steady" / "first")
+    marches the batch in slot s ^ 1 ahead on the side stream, joined before the graph ends.  Kinds: "first" marches its own
+    batch in line (first step, step after an occupancy update), "last" marches nothing ahead (step before an update),
+    "steady" finds its samples marched by the previous replay.  A change of the loss scale (step guard) or of the workspace
+    (capacity growth) drops the captured graphs; they are re-captured on the next step.
+    """
+
+    def __init__(self, engine):
+        assert engine.world == 1, "graph replay is implemented for single-process engines"
+        self.e = engine
+        n, dev = engine.n_rays, engine.device
+        self.slots = [tuple(torch.zeros(n, 3, device=dev) for _ in range(3)) for _ in range(2)]
+        self.graphs, self.launches = {}, {}
+        self._key = None
+        self._lr_pin = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self._pool = None
+        self._warm = False
+        self.replays = 0
+        # hybrid: the graphs hold the parameter-dependent chain only and the marching stays an eager side-stream launch (host
+        # 0.18 instead of 0.12 ms/step; same device time unless something -- the benchmark's L2 flush -- sits between replays)
+        self.hybrid = os.environ.get("RNB_GRAPH_HYBRID", "0") == "1"
+
+    def load(self, slot, rays_o=None, rays_d=None, target_rgb=None):
+        """Copy (parts of) a batch into static slot `slot` on the current stream (device or pinned-host sources)."""
+        for dst, src in zip(self.slots[slot], (rays_o, rays_d, target_rgb)):
+            if src is not None:
+                dst.copy_(src, non_blocking=True)
+
+    def _body(self, slot, kind):
+        e = self.e
+        o, d, t = self.slots[slot]
+        if kind == "first":
+            e._ahead.clear()
+        nxt = None if kind == "last" else self.slots[slot ^ 1][:2]
+        e._force_slot = slot
+        try:
+            e.forward_backward(o, d, t, None, e.background(False), True, nxt)
+        finally:
+            e._force_slot = None
+        e.adam_step(lr_from_device=True)
+        if nxt is not None and torch.cuda.is_current_stream_capturing():
+            # a capture must end with every forked stream joined: the march of the next batch ends inside this graph
+            torch.cuda.current_stream(e.device).wait_event(e._ahead[(nxt[0].data_ptr(), nxt[1].data_ptr())][4])
+
+    def _set_lr(self, lr, force=False):
+        e = self.e
+        v = float(e.lr if lr is None else lr)
+        if force or v != getattr(self, "_lr_dev", None):       # (a constant rate is written once)
+            self._lr_pin = torch.tensor([v], dtype=torch.float32).pin_memory()      # fresh pinned word: the previous copy may be in flight
+            e.status[8:9].view(torch.float32).copy_(self._lr_pin, non_blocking=True)
+            self._lr_dev = v
+
+    def _capture(self, slot, kind):
+        e = self.e
+        g = torch.cuda.CUDAGraph()
+        saved, n_before, l_before = dict(e._ahead), e.opt_step, _lib.launch_count
+        o, d, _ = self.slots[slot]
+        ev = torch.cuda.Event()
+        # the bookkeeping of marched-ahead batches must look, at capture time, like it will at replay time
+        e._ahead = {} if kind == "first" else {(o.data_ptr(), d.data_ptr()): (slot, o, d, None, ev)}
+        torch.cuda.synchronize(e.device)
+        if getattr(self, "_cap_stream", None) is None:
+            # kernel nodes inherit the priority of the stream they were captured on: the step's own chain is captured at high
+            # priority, so the side-stream work (next batch's march) only fills what the chain leaves free -- as in the eager
+            # step, which the caller runs on a high-priority stream
+            self._cap_stream = torch.cuda.Stream(e.device, priority=-1)
+        with torch.cuda.graph(g, pool=self._pool, stream=self._cap_stream, capture_error_mode="thread_local"):
+            if kind != "first":
+                ev.record()        # stands for "the previous replay's march is complete" (it is: replays are stream-ordered)
+            self._body(slot, kind)
+        self._pool = self._pool or g.pool()
+        e.opt_step, e._ahead = n_before, saved          # capturing enqueues nothing
+        self.launches[(slot, kind)] = _lib.launch_count - l_before
+        _lib.launch_count = l_before
+        return g
+
+    def step(self, slot, lr=None, kind="steady"):
+        """Train on the batch in static slot `slot`; unless kind == "last", march the batch in slot ^ 1 ahead (it must have
+        been loaded).  Returns the engine's loss vector view."""
+        e = self.e
+        e.sync_params()
+        e._poll_guard()
+        key = (e.cfg.loss_scale, e.ws.data_ptr())       # both are baked into the graphs
+        if key != self._key:
+            self.graphs.clear(); self._key = key; self._lr_dev = None      # (a new workspace has a fresh status block)
+        cur = torch.cuda.current_stream(e.device)
+        self._set_lr(lr)
+        if not self._warm:
+            # the library sets kernel attributes lazily and the engine creates its side streams on first use: one eager step
+            self._body(slot, kind); self._warm = True; self.replays += 1
+            if e.opt_step % e.status_interval == 0:
+                e._post_status()
+            return e.loss
+        if self.hybrid:
+            # graphs hold the parameter-dependent chain only (field, compositing, losses, backward, Adam: kind "last"); the
+            # marching of this batch (kind "first") and of the next one stays an eager launch on the side stream
+            if kind == "first":
+                for rec in e._ahead.values():
+                    cur.wait_event(rec[4])
+                e._ahead.clear()
+                e.prefetch(self.slots[slot][0], self.slots[slot][1], slot=slot)
+            mine = e._ahead.pop((self.slots[slot][0].data_ptr(), self.slots[slot][1].data_ptr()), None)
+            if mine is not None:
+                cur.wait_event(mine[4])
+            if kind != "last":
+                while len(e._ahead) > 0:
+                    cur.wait_event(e._ahead.pop(next(iter(e._ahead)))[4])
+                e.prefetch(self.slots[slot ^ 1][0], self.slots[slot ^ 1][1], slot=slot ^ 1)
+            gk = (slot, "last")
+            if gk not in self.graphs:
+                keep = dict(e._ahead)
+                self.graphs[gk] = self._capture(slot, "last")
+                e._ahead = keep
+            self.graphs[gk].replay()
+            _lib.launch_count += self.launches[gk]
+            e.opt_step += 1
+            e._slot = slot
+            self.replays += 1
+            if e.opt_step % e.status_interval == 0:
+                e._post_status()
+            return e.loss
+        gk = (slot, kind)
+        if gk not in self.graphs:
+            self.graphs[gk] = self._capture(slot, kind)
+        for rec in e._ahead.values():          # a batch marched ahead by an EAGER step (the warm-up): order the replay behind it
+            cur.wait_event(rec[4])
+        e._ahead.clear()
+        self.graphs[gk].replay()
+        _lib.launch_count += self.launches[gk]
+        e.opt_step += 1
+        e._slot = slot
+        self.replays += 1
+        if e.opt_step % e.status_interval == 0:
+            e._post_status()
+        return e.loss

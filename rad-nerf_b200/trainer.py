@@ -34,7 +34,7 @@ class Trainer:
     def __init__(self, scale=0.5, K=2, lr=1e-2, log2_T=19, lambda_opacity=1e-3, lambda_cv=1e-2, lambda_dm=5e-3,
                  loss_scale=1024.0, device="cuda", update_interval=16, warmup_steps=256, freeze_occupancy=False,
                  random_bg=False, seed=0, engine=True, batch_rays=8192, samples_per_ray=128, total_steps=None,
-                 on_overflow="grow"):
+                 on_overflow="grow", graph=False):
         self.device = torch.device(device)
         self.K, self.scale = K, scale
         self.exp_step_factor = syn.exp_step_factor_for_scale(scale)
@@ -68,6 +68,9 @@ class Trainer:
             self.engine = Engine(self.model, self.gate, n_rays=batch_rays, exp_step_factor=self.exp_step_factor,
                                  samples_per_ray=samples_per_ray, lambda_opacity=lambda_opacity, lambda_cv=lambda_cv,
                                  lambda_dm=lambda_dm, lr=lr, on_overflow=on_overflow)
+        # graph=True: the step is replayed from captured CUDA graphs (engine.GraphStepper); batches pass through two static slots
+        self.stepper = self.engine.graph_stepper() if (graph and self.engine is not None and self.world == 1 and not random_bg) else None
+        self._slot, self._staged = 0, None
 
     # -- occupancy ---------------------------------------------------------------------------
     def set_occupancy(self, bitfields):
@@ -108,6 +111,35 @@ class Trainer:
             self._shadow[n] = getattr(self.model, n)
             setattr(self.model, n, keep[n])
 
+    def _graph_step(self, rays_o, rays_d, target_rgb, next_rays):
+        """One step through the captured graphs.  next_rays = (rays_o, rays_d[, target_rgb]) of the FOLLOWING step: staged
+        into the other static slot so that this step's graph can march it ahead.  `_staged` = (slot, has_target)."""
+        st, s = self.stepper, self._slot
+        if self._staged is not None and self._staged[0] == s:      # the rays are in place (marched by the previous graph)
+            if not self._staged[1]:
+                st.load(s, None, None, target_rgb)
+            first = False
+        else:
+            st.load(s, rays_o, rays_d, target_rgb)
+            first = True
+        after_update = self.global_step % self.update_interval == 0
+        before_update = (self.global_step + 1) % self.update_interval == 0
+        look_ahead = next_rays is not None and not before_update
+        kind = ("first" if (first or after_update) else "steady") if look_ahead else "last"
+        if kind == "last" and (first or after_update):
+            # nothing marched ahead for this batch and nothing to march ahead: the plain eager step
+            self.engine._ahead.clear()
+            loss = self.engine.step(self.stepper.slots[s][0], self.stepper.slots[s][1], self.stepper.slots[s][2], lr=self.lr)
+        else:
+            if look_ahead:
+                st.load(s ^ 1, *next_rays)
+            loss = st.step(s, lr=self.lr, kind=kind)
+        self._staged = (s ^ 1, len(next_rays) > 2) if look_ahead else None
+        self._slot = s ^ 1
+        self.global_step += 1
+        self._last_results = None
+        return loss[0]
+
     @property
     def last_results(self):
         """The reference's result dict of the last step (ml_rendering.py:72-77)."""
@@ -127,6 +159,8 @@ class Trainer:
             self.lr = cosine_lr(self.base_lr, self.global_step, self.total_steps)
             for g in self.opt.param_groups:
                 g["lr"] = self.lr
+        if self.stepper is not None:
+            return self._graph_step(rays_o, rays_d, target_rgb, next_rays)
         if self.engine is not None:
             if next_rays is not None and (self.global_step + 1) % self.update_interval == 0:
                 next_rays = None
