@@ -442,7 +442,9 @@ typedef struct {
 int rnb_render_layout_of(const rnb_engine_config* cfg, rnb_render_layout* out);
 /* out: rgb (R,3), depth (R,K) ungated (Q19), opacity (R); pass_rgb (K,R,3) per-sub-NeRF colours after the
  * background blend (may be NULL); stats_host[2] = {samples evaluated, rounds} (may be NULL).  bg_host (K,3).
- * Synchronises the stream once per round (the reference: twice per round and sub-NeRF). */
+ * Rounds are planned on the device and launched without read-backs (the reference: two host synchronisations per round and
+ * sub-NeRF); the call synchronises the stream ONCE, at its end (statistics).  First call per host thread: 1 KB of pinned
+ * memory and two events are created and kept. */
 int rnb_render(const rnb_engine_config* cfg, void* workspace, const void* params_f16, const float* rays_o,
                const float* rays_d, const uint8_t* const* bitfields, const float* bg_host, float* rgb, float* depth,
                float* opacity, float* pass_rgb, int64_t* stats_host, rnb_stream_t stream);

@@ -20,15 +20,17 @@ void set_error(const char* fmt, ...);
 
 inline cudaStream_t as_stream(rnb_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
-inline int check_launch(const char* what) {
+inline int check_launch_at(const char* what, const char* file, int line) {
   cudaError_t e = cudaPeekAtLastError();
   if (e != cudaSuccess) {
     cudaGetLastError();  // clear the (non-sticky) error
-    set_error("%s: %s", what, cudaGetErrorString(e));
+    set_error("%s: %s [%s:%d]", what, cudaGetErrorString(e), file, line);
     return RNB_ERR_LAUNCH;
   }
   return RNB_OK;
 }
+
+#define check_launch(what) check_launch_at(what, __FILE__, __LINE__)
 
 #define RNB_REQUIRE(cond, what)                         \
   do {                                                  \
@@ -42,7 +44,7 @@ inline int check_launch(const char* what) {
   do {                                                                    \
     cudaError_t e__ = (call);                                             \
     if (e__ != cudaSuccess) {                                             \
-      ::rnb::set_error("%s: %s", what, cudaGetErrorString(e__));          \
+      ::rnb::set_error("%s: %s [%s:%d]", what, cudaGetErrorString(e__), __FILE__, __LINE__); \
       return RNB_ERR_LAUNCH;                                              \
     }                                                                     \
   } while (0)

@@ -186,6 +186,7 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
     int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
     if (pass_end > A.capacity) pass_end = A.capacity;
     const int64_t n_tiles = pass_end > base ? (pass_end - base + kRows - 1) / kRows : 0;
+    if (n_tiles == 0) continue;      // (CTA-uniform) an empty pass -- e.g. every round behind the end of a frame -- costs nothing
     // ---- stage this pass's weights (whole CTA) ----
     __syncthreads();
     {

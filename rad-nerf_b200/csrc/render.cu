@@ -16,6 +16,8 @@
 // 8 (Q13: the schedule only matters for the 1024-scheduled-samples cut-off).
 #include <stdlib.h>
 
+#include <vector>
+
 #include "aabb.cuh"
 #include "composite.cuh"
 #include "march_warp.cuh"
@@ -24,7 +26,16 @@
 namespace rnb {
 
 struct BitfieldPtrsR { const uint8_t* p[RNB_MAX_K]; };
-struct PassCounts { int32_t n[RNB_MAX_K]; int32_t base[RNB_MAX_K + 1]; };   // alive items / sample-region base per pass
+// The plan of one round, in device memory: written by inf_plan_kernel from the previous round's survivors, read by the
+// round's kernels.  The host launches rounds without knowing how many rays are alive (no read-back per round).
+struct PassCounts {
+  int32_t n[RNB_MAX_K]; int32_t base[RNB_MAX_K + 1];   // alive items / sample-region base per pass
+  int32_t NS;               // sample budget per item in this round (ml_rendering.py:115)
+  int32_t scheduled;        // budgets handed out so far (the reference's `samples`, ml_rendering.py:111-116)
+  int32_t done;             // no ray alive or the 1024 scheduled samples are spent: every later launch returns at once
+  int32_t rounds;           // rounds planned so far
+  long long total_samples;  // samples evaluated (statistics)
+};
 
 struct InfState {
   float* t_cur; float* t2; float* opacity; float* depth; float* rgb;   // (K*R), rgb (K*R,3)
@@ -36,7 +47,8 @@ struct InfState {
 
 // all (pass, ray) items alive; scene-box interval + NEAR_DISTANCE clamp (ml_rendering.py:48-50)
 __global__ void __launch_bounds__(256) inf_init_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, int R, int K,
-                                                       float cx, float cy, float cz, float hx, float hy, float hz, float near_d, InfState S) {
+                                                       float cx, float cy, float cz, float hx, float hy, float hz, float near_d, InfState S,
+                                                       PassCounts* __restrict__ plan) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R) return;
   const float ox = rays_o[3 * r], oy = rays_o[3 * r + 1], oz = rays_o[3 * r + 2];
@@ -50,12 +62,38 @@ __global__ void __launch_bounds__(256) inf_init_kernel(const float* __restrict__
     S.t_cur[i] = t1; S.t2[i] = t2; S.opacity[i] = 0.f; S.depth[i] = 0.f;
     S.rgb[3 * i] = 0.f; S.rgb[3 * i + 1] = 0.f; S.rgb[3 * i + 2] = 0.f;
     S.alive[0][i] = r;
-    if (r == 0) S.alive_cnt[0][p] = R;
+    if (r == 0) { S.alive_cnt[0][p] = R; S.sample_cnt[p] = 0; }
   }
+  if (r == 0) { plan->NS = 0; plan->scheduled = 0; plan->done = 0; plan->rounds = 0; plan->total_samples = 0; }
 }
 
-__global__ void inf_round_begin_kernel(InfState S, int K, int out) {
-  if (threadIdx.x < K) { S.sample_cnt[threadIdx.x] = 0; S.alive_cnt[out][threadIdx.x] = 0; }
+// One thread plans the round: N_samples = max(min(N_rays // N_alive, 64), min_samples) (ml_rendering.py:115) with a floor set
+// by the workspace the caller provided (samples per alive item and round that always fit: 8..64; a warp computes 32 chain
+// elements at a time, so small budgets re-do marching work round after round), shrunk until the round's samples fit.
+__global__ void inf_plan_kernel(PassCounts* __restrict__ C, InfState S, int K, int R, int in, int max_samples, int min_samples,
+                                int ns_floor, int64_t capacity) {
+  if (threadIdx.x != 0 || C->done) return;
+  int64_t alive = 0;
+  for (int p = 0; p < K; p++) { C->total_samples += S.sample_cnt[p]; S.sample_cnt[p] = 0; alive += S.alive_cnt[in][p]; }
+  if (C->scheduled >= max_samples || alive == 0) { C->done = 1; return; }
+  int64_t NS = ((int64_t)K * R) / alive;
+  if (NS > 64) NS = 64;
+  if (NS < min_samples) NS = min_samples;
+  if (NS < ns_floor) NS = ns_floor;
+  while (NS > 1) {
+    int64_t need = 0;
+    for (int p = 0; p < K; p++) need += ((int64_t)S.alive_cnt[in][p] * NS + 127) / 128 * 128;
+    if (need <= capacity) break;
+    NS--;
+  }
+  int64_t base = 0;
+  for (int p = 0; p < K; p++) {
+    C->n[p] = S.alive_cnt[in][p];
+    C->base[p] = (int32_t)base; base += ((int64_t)C->n[p] * NS + 127) / 128 * 128;
+    S.alive_cnt[in ^ 1][p] = 0;
+  }
+  C->base[K] = (int32_t)base;
+  C->NS = (int32_t)NS; C->scheduled += (int32_t)NS; C->rounds += 1;
 }
 
 // flat alive-item index -> (pass, position in the pass's list)
@@ -70,10 +108,16 @@ __device__ __forceinline__ bool locate_item(const PassCounts& C, int K, int64_t 
 
 template <bool kConstDt, bool kOneCascade>
 __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, MarchParams mp,
-                                                        BitfieldPtrsR bf, PassCounts C, int K, int R, int in, int NS, int64_t capacity,
-                                                        InfState S, int32_t* __restrict__ ray_id, float* __restrict__ ts,
-                                                        const uint64_t* __restrict__ coarse) {
+                                                        BitfieldPtrsR bf, const PassCounts* __restrict__ plan, int K, int R, int in,
+                                                        int64_t capacity, InfState S, int32_t* __restrict__ ray_id,
+                                                        float* __restrict__ ts, const uint64_t* __restrict__ coarse_grid) {
   __shared__ float tbuf[8][64];
+  __shared__ PassCounts C;
+  if (plan->done) return;
+  if (threadIdx.x == 0) C = *plan;
+  __syncthreads();
+  const int NS = C.NS;
+  const uint64_t* coarse = C.rounds == 1 ? coarse_grid : nullptr;      // the empty-space test runs in the first round only
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   int64_t total = 0;
   for (int p = 0; p < K; p++) total += C.n[p];
@@ -111,16 +155,21 @@ __global__ void __launch_bounds__(256) inf_march_kernel(const float* __restrict_
 }
 
 // seg for rnb_field_fwd: pass bases (host-planned upper bounds) and the sample counts actually reserved
-__global__ void inf_seg_kernel(PassCounts C, int K, const int32_t* __restrict__ sample_cnt, int32_t* __restrict__ seg) {
+__global__ void inf_seg_kernel(const PassCounts* __restrict__ C, int K, const int32_t* __restrict__ sample_cnt, int32_t* __restrict__ seg) {
   const int p = threadIdx.x;
-  if (p < K) { seg[p] = C.base[p]; seg[K + 1 + p] = sample_cnt[p]; }
-  if (p == 0) seg[K] = C.base[K];
+  const bool done = C->done != 0;       // finished frame: an empty sample list (the field kernel then has nothing to do)
+  if (p < K) { seg[p] = done ? 0 : C->base[p]; seg[K + 1 + p] = done ? 0 : sample_cnt[p]; }
+  if (p == 0) seg[K] = done ? 0 : C->base[K];
 }
 
 // Resume-able compositing of one round (volumerendering.cu:223-249), warp per alive item.
 __global__ void __launch_bounds__(256) inf_composite_kernel(const float* __restrict__ sigmas, const __half* __restrict__ rgb4,
-                                                            const float* __restrict__ ts, MarchParams mp, PassCounts C, int K, int R,
-                                                            int in, float T_threshold, int64_t capacity, InfState S) {
+                                                            const float* __restrict__ ts, MarchParams mp, const PassCounts* __restrict__ plan,
+                                                            int K, int R, int in, float T_threshold, int64_t capacity, InfState S) {
+  __shared__ PassCounts C;
+  if (plan->done) return;
+  if (threadIdx.x == 0) C = *plan;
+  __syncthreads();
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   int64_t total = 0;
   for (int p = 0; p < K; p++) total += C.n[p];
@@ -205,7 +254,8 @@ int rnb_render_layout_of(const rnb_engine_config* c, rnb_render_layout* L) {
   L->gate_in = take(R * 16 * 2); L->gate_logits = take(R * 16 * 2); L->gate_prob = take(R * K * 4); L->importance = take(RNB_MAX_K * 4);
   L->t_cur = take(K * R * 4); L->t2 = take(K * R * 4); L->acc_opacity = take(K * R * 4); L->acc_depth = take(K * R * 4);
   L->acc_rgb = take(K * R * 12); L->item_start = take(K * R * 4); L->item_n = take(K * R * 4);
-  L->alive0 = take(K * R * 4); L->alive1 = take(K * R * 4); L->counters = take(4 * RNB_MAX_K * 4);
+  L->alive0 = take(K * R * 4); L->alive1 = take(K * R * 4);
+  L->counters = take(512);      // alive counts (2 x K), sample counts (K); at byte 256: the round plan
   L->seg = take((2 * RNB_MAX_K + 4) * 4);
   L->ray_id = take(S * 4); L->ts = take(S * 4); L->sigmas = take(S * 4); L->rgb4 = take(S * 8);
   L->coarse = take((int64_t)K * c->cascades * kCoarseWords * 8);
@@ -248,85 +298,89 @@ int rnb_render(const rnb_engine_config* c, void* workspace, const void* params_f
     coarse = (uint64_t*)(ws + L.coarse);
     if (int rc = coarse_build(bitfields, K, c->cascades, coarse, st)) return rc;
   }
+  PassCounts* plan = reinterpret_cast<PassCounts*>(ws + L.counters + 256);
+  static_assert(sizeof(PassCounts) <= 256 && 3 * RNB_MAX_K * 4 <= 256, "round plan fits the counters region");
   inf_init_kernel<<<ceil_div(R, 256), 256, 0, st>>>(rays_o, rays_d, R, K, c->center[0], c->center[1], c->center[2], c->half_size[0],
-                                                    c->half_size[1], c->half_size[2], c->near_distance, St);
+                                                    c->half_size[1], c->half_size[2], c->near_distance, St, plan);
   rnb_field_params P;
   P.K = K; P.grid = c->grid;
   for (int k = 0; k < 3; k++) { P.xyz_min[k] = c->xyz_min[k]; P.xyz_max[k] = c->xyz_max[k]; }
   P.table_f16 = p16 + c->table_off;
   for (int i = 0; i < K; i++) { P.geo_w_f16[i] = p16 + c->geo_off[i]; P.rgb_w_f16[i] = p16 + c->rgb_off[i]; }
-  PassCounts C;
-  for (int p = 0; p < K; p++) C.n[p] = R;
   const int min_samples = c->exp_step_factor == 0.0f ? 1 : 4;   // ml_rendering.py:108
   int64_t ns_floor = (S - 128 * (int64_t)K) / ((int64_t)K * R);
   ns_floor = ns_floor < 8 ? 8 : ns_floor > 64 ? 64 : ns_floor;
   // RNB_RENDER_PROF=1: per-stage device time of this call on stderr (CUDA events; diagnostics only)
   const bool prof = getenv("RNB_RENDER_PROF") != nullptr;
-  float t_march = 0.f, t_field = 0.f, t_comp = 0.f;
-  cudaEvent_t ev[4];
-  if (prof) for (int i = 0; i < 4; i++) cudaEventCreate(&ev[i]);
-  int scheduled = 0, in = 0, rounds = 0;
-  int64_t total_samples = 0;
-  while (scheduled < c->max_samples) {
-    int64_t alive = 0;
-    for (int p = 0; p < K; p++) alive += C.n[p];
-    if (alive == 0) break;
-    // N_samples = max(min(N_rays // N_alive, 64), min_samples) (ml_rendering.py:115) with a floor set by the workspace the
-    // caller provided (samples per alive item and round that always fit: 8..64).  A warp computes 32 chain elements at a
-    // time, so small budgets re-do marching work round after round; large ones evaluate samples behind a termination.
-    int64_t NS = ((int64_t)K * R) / alive;
-    if (NS > 64) NS = 64;
-    if (NS < min_samples) NS = min_samples;
-    if (NS < ns_floor) NS = ns_floor;
-    while (NS > 1) {
-      int64_t need = 0;
-      for (int p = 0; p < K; p++) need += ((int64_t)C.n[p] * NS + 127) / 128 * 128;
-      if (need <= S) break;
-      NS--;
-    }
-    scheduled += (int)NS;
-    int64_t base = 0;
-    for (int p = 0; p < K; p++) { C.base[p] = (int32_t)base; base += ((int64_t)C.n[p] * NS + 127) / 128 * 128; }
-    C.base[K] = (int32_t)base;
-    if (prof) cudaEventRecord(ev[0], st);
-    inf_round_begin_kernel<<<1, 32, 0, st>>>(St, K, in ^ 1);
-    int grid = ceil_div(alive, 8);
-    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
-#define RNB_INF_MARCH(CONST_DT, ONE)                                                                                  \
-  inf_march_kernel<CONST_DT, ONE><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, C, K, R, in, (int)NS, S, St, ray_id, ts, \
-                                                        rounds == 0 ? coarse : nullptr)
-    if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_INF_MARCH(true, true);
-    else if (c->exp_step_factor == 0.0f) RNB_INF_MARCH(true, false);
-    else RNB_INF_MARCH(false, false);
-#undef RNB_INF_MARCH
-    inf_seg_kernel<<<1, 32, 0, st>>>(C, K, St.sample_cnt, seg);
-    if (int rc = check_launch(what)) return rc;
-    rnb_samples Sm = {rays_o, rays_d, ray_id, ts, seg, base > 0 ? base : 128};
-    if (prof) cudaEventRecord(ev[1], st);
-    if (int rc = rnb_field_fwd(&P, &Sm, nullptr, sigmas, rgb4, stream)) return rc;
-    if (prof) cudaEventRecord(ev[2], st);
-    inf_composite_kernel<<<grid, 256, 0, st>>>(sigmas, rgb4, ts, mp, C, K, R, in, c->T_threshold, S, St);
-    if (int rc = check_launch(what)) return rc;
-    int32_t host_cnt[2 * RNB_MAX_K + RNB_MAX_K];
-    RNB_CUDA(cudaMemcpyAsync(host_cnt, counters, sizeof(int32_t) * 3 * RNB_MAX_K, cudaMemcpyDeviceToHost, st), what);
-    if (prof) cudaEventRecord(ev[3], st);
-    RNB_CUDA(cudaStreamSynchronize(st), what);
-    if (prof) {
-      float a = 0.f, b = 0.f, c2 = 0.f;
-      cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]); cudaEventElapsedTime(&c2, ev[2], ev[3]);
-      t_march += a; t_field += b; t_comp += c2;
-    }
-    in ^= 1;
-    for (int p = 0; p < K; p++) { C.n[p] = host_cnt[in * RNB_MAX_K + p]; total_samples += host_cnt[2 * RNB_MAX_K + p]; }
-    rounds++;
+  std::vector<cudaEvent_t> pev;
+  auto mark = [&]() { if (prof) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); pev.push_back(e); } };
+  // The reference's loop (ml_rendering.py:108-141) reads the number of alive rays back twice per iteration and sub-NeRF.
+  // Here a round is planned ON THE DEVICE (inf_plan_kernel) and the host launches rounds without waiting: kBatch rounds
+  // at a time, with an asynchronous copy of the plan's `done` flag behind every batch that is looked at only after the NEXT
+  // batch has been enqueued -- the GPU never idles on the host, and a finished frame costs at most 2 * kBatch - 1 empty
+  // rounds (four kernels each that return at once) before the host notices.
+  struct Pinned { int32_t* p = nullptr; cudaEvent_t ev[2] = {nullptr, nullptr}; };
+  static thread_local Pinned pin;       // 1 KB of pinned memory and two events per calling thread, created once
+  if (pin.p == nullptr) {
+    RNB_CUDA(cudaHostAlloc((void**)&pin.p, 1024, cudaHostAllocDefault), what);
+    RNB_CUDA(cudaEventCreateWithFlags(&pin.ev[0], cudaEventDisableTiming), what);
+    RNB_CUDA(cudaEventCreateWithFlags(&pin.ev[1], cudaEventDisableTiming), what);
   }
+  const int kBatch = 4;
+  const int max_rounds = c->max_samples;      // a round schedules at least one sample: the loop below ends on `done` long before
+  const int grid = kNumSMs * 8;
+  rnb_samples Sm = {rays_o, rays_d, ray_id, ts, seg, S};
+  int launched = 0, batches = 0;
+  bool finished = false;
+  while (!finished && launched < max_rounds + 2 * kBatch) {
+    for (int b = 0; b < kBatch; b++, launched++) {
+      const int in = launched & 1;
+      mark();
+      inf_plan_kernel<<<1, 32, 0, st>>>(plan, St, K, R, in, c->max_samples, min_samples, (int)ns_floor, S);
+#define RNB_INF_MARCH(CONST_DT, ONE) \
+  inf_march_kernel<CONST_DT, ONE><<<grid, 256, 0, st>>>(rays_o, rays_d, mp, bf, plan, K, R, in, S, St, ray_id, ts, coarse)
+      if (c->exp_step_factor == 0.0f && c->cascades == 1) RNB_INF_MARCH(true, true);
+      else if (c->exp_step_factor == 0.0f) RNB_INF_MARCH(true, false);
+      else RNB_INF_MARCH(false, false);
+#undef RNB_INF_MARCH
+      inf_seg_kernel<<<1, 32, 0, st>>>(plan, K, St.sample_cnt, seg);
+      if (int rc = check_launch(what)) return rc;
+      mark();
+      if (int rc = rnb_field_fwd(&P, &Sm, nullptr, sigmas, rgb4, stream)) return rc;
+      mark();
+      inf_composite_kernel<<<grid, 256, 0, st>>>(sigmas, rgb4, ts, mp, plan, K, R, in, c->T_threshold, S, St);
+      if (int rc = check_launch(what)) return rc;
+      mark();
+    }
+    RNB_CUDA(cudaMemcpyAsync(pin.p + 16 * (batches & 1), &plan->done, 4, cudaMemcpyDeviceToHost, st), what);
+    RNB_CUDA(cudaEventRecord(pin.ev[batches & 1], st), what);
+    if (batches > 0) {      // the PREVIOUS batch's flag: that batch has long finished
+      RNB_CUDA(cudaEventSynchronize(pin.ev[(batches - 1) & 1]), what);
+      finished = pin.p[16 * ((batches - 1) & 1)] != 0;
+    }
+    batches++;
+  }
+  // the plan of the round that found nothing alive carries the totals
+  inf_plan_kernel<<<1, 32, 0, st>>>(plan, St, K, R, launched & 1, c->max_samples, min_samples, (int)ns_floor, S);
+  static_assert(256 + sizeof(PassCounts) <= 1024, "pinned block");
+  RNB_CUDA(cudaMemcpyAsync(pin.p + 64, plan, sizeof(PassCounts), cudaMemcpyDeviceToHost, st), what);
   BgR bg;
   for (int i = 0; i < K; i++) for (int k = 0; k < 3; k++) bg.c[i][k] = bg_host[3 * i + k];
   inf_finish_kernel<<<ceil_div(R, 256), 256, 0, st>>>(St, (const float*)(ws + L.gate_prob), bg, R, K, rgb, depth, opacity, pass_rgb);
+  RNB_CUDA(cudaStreamSynchronize(st), what);      // one synchronisation per frame: the statistics (and the pinned words are free again)
+  const PassCounts* fin = reinterpret_cast<const PassCounts*>(pin.p + 64);
+  const int rounds = fin->rounds;
+  const int64_t total_samples = fin->total_samples;
   if (prof) {
-    fprintf(stderr, "[rnb_render] rays %d K %d rounds %d samples %lld: march %.3f ms, field %.3f ms, composite+readback %.3f ms\n", R, K, rounds,
-            (long long)total_samples, t_march, t_field, t_comp);
-    for (int i = 0; i < 4; i++) cudaEventDestroy(ev[i]);
+    float t_march = 0.f, t_field = 0.f, t_comp = 0.f;
+    for (size_t i = 0; i + 3 < pev.size(); i += 4) {
+      float a = 0.f, b2 = 0.f, c2 = 0.f;
+      cudaEventElapsedTime(&a, pev[i], pev[i + 1]); cudaEventElapsedTime(&b2, pev[i + 1], pev[i + 2]); cudaEventElapsedTime(&c2, pev[i + 2], pev[i + 3]);
+      t_march += a; t_field += b2; t_comp += c2;
+    }
+    fprintf(stderr, "[rnb_render] rays %d K %d rounds %d (launched %d) samples %lld: plan+march %.3f ms, field %.3f ms, composite %.3f ms\n", R, K,
+            rounds, launched, (long long)total_samples, t_march, t_field, t_comp);
+    for (cudaEvent_t e : pev) cudaEventDestroy(e);
   }
   if (stats_host) { stats_host[0] = total_samples; stats_host[1] = rounds; }
   return check_launch(what);

@@ -13,7 +13,10 @@ from bench import scene_bitfields, workload  # noqa: E402
 
 
 def main():
-    name = sys.argv[1] if len(sys.argv) > 1 else "radnerf_tat_k8_infer"
+    fitted = "--fitted" in sys.argv
+    names = [a for a in sys.argv[1:] if not a.startswith("--")]
+    name = names[0] if names else "radnerf_tat_k8_infer"
+    spr = int(os.environ.get("RNB_RENDER_SPR", "32"))
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
@@ -23,6 +26,24 @@ def main():
     syn, w = workload(name)
     tr = Trainer(scale=w["scale"], K=w["K"], freeze_occupancy=True, device=f"cuda:{local}", engine=True, batch_rays=8192)
     tr.set_occupancy(scene_bitfields(syn, w))
+    if fitted:
+        # rank 0 trains 2000 steps on the analytic scene; parameters and occupancy are broadcast (SURVEY 8d "fitted" state)
+        eng = tr.engine
+        if rank == 0:
+            sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+            from fit_scene import fit
+            _, src = fit(steps=2000, K=w["K"], return_trainer=True)
+            with torch.no_grad():
+                eng.flat.copy_(src.engine.flat)
+                for a, b in zip(eng.grids() + eng.bitfields(), src.engine.grids() + src.engine.bitfields()):
+                    a.copy_(b)
+            del src
+        if world > 1:
+            for t in [eng.flat] + eng.grids() + eng.bitfields():
+                dist.broadcast(t, 0)
+        for _, m in eng._mods:
+            m._shadow.version = None
+        eng.sync_params()
     cam = syn.make_cameras(100, w["radius"], w["H"], w["W"], w["fx"])
     H, W = w["H"], w["W"]
     o, d = syn.full_image_rays(cam, 3)
@@ -31,7 +52,7 @@ def main():
     o = torch.from_numpy(o)[sel].contiguous().cuda(); d = torch.from_numpy(d)[sel].contiguous().cuda()
 
     def frame():
-        res = tr.engine.render(o, d)
+        res = tr.engine.render(o, d, samples_per_ray=spr)
         out = torch.cat([res["rgb"], res["opacity"][:, None], res["depth"]], 1)      # (3 + 1 + K) floats per ray
         return parallel.gather_frame(out, H, W), res
 
@@ -52,7 +73,7 @@ def main():
         dist.all_reduce(smp)
     if rank == 0:
         assert full.shape == (H * W, 4 + w["K"]) and bool(torch.isfinite(full).all())
-        print(json.dumps({"workload": name, "n_gpus": world, "rays": H * W, "K": w["K"], "frame_ms": round(float(ms), 3),
+        print(json.dumps({"workload": name, "params": "fitted (2000 steps)" if fitted else "random init", "samples_per_round": spr, "n_gpus": world, "rays": H * W, "K": w["K"], "frame_ms": round(float(ms), 3),
                           "samples": int(smp), "Msamples_per_s": round(float(smp) / float(ms) / 1e3, 1),
                           "sharding": "interleaved rows, all_gather of (3+1+K) floats per ray"}), flush=True)
     if world > 1:

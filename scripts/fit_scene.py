@@ -15,7 +15,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def fit(steps=2000, K=2, res=200, batch=8192, n_train=60, n_test=4, log_every=0, seed=0, log2_T=19):
+def fit(steps=2000, K=2, res=200, batch=8192, n_train=60, n_test=4, log_every=0, seed=0, log2_T=19, return_trainer=False):
     from radnerf_b200 import synthetic as syn
     from radnerf_b200.data import RaySampler, get_ray_directions
     from radnerf_b200.trainer import Trainer
@@ -59,10 +59,11 @@ def fit(steps=2000, K=2, res=200, batch=8192, n_train=60, n_test=4, log_every=0,
     test_psnr = psnr_of(test_ids)
     train_psnr = psnr_of([0, 1])
     occ = [float((b != 0).float().mean()) for b in tr.engine.bitfields()]
-    return {"steps": steps, "K": K, "res": res, "batch": batch, "train_views": n_train, "train_seconds": round(train_s, 2),
+    info = {"steps": steps, "K": K, "res": res, "batch": batch, "train_views": n_train, "train_seconds": round(train_s, 2),
             "rays_per_s": round(steps * batch / train_s), "final_loss": float(loss), "psnr_test": [round(p, 2) for p in test_psnr],
             "psnr_test_mean": round(sum(test_psnr) / len(test_psnr), 2), "psnr_train_views": [round(p, 2) for p in train_psnr],
             "occupied_bitfield_bytes_frac": [round(x, 4) for x in occ], "loss_curve": curve}
+    return (info, tr) if return_trainer else info
 
 
 if __name__ == "__main__":
