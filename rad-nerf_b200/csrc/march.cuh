@@ -6,6 +6,8 @@
 // verified against the SASS of the reference built for sm_100a (DESIGN.md "FMA placement").
 // That is what makes per-ray sample counts / offsets bit-exact (BASELINE.json north_star).
 #pragma once
+#include <string.h>
+
 #include "common.cuh"
 
 namespace rnb {
@@ -23,6 +25,7 @@ struct MarchParams {
   float esf;         // exp_step_factor
   float dt_min;      // SQRT3 / max_samples                         (raymarching.cu:12)
   float dt_max;      // SQRT3*2*dt_scale / grid_size, dt_scale = scale (train) or cascades (test, Q1)
+  int pow2_scale;    // scale is a power of two: every mip bound min(2^(mip-1), scale) is one, and 1 / bound is an exponent flip
 };
 
 // host side: IEEE fp32 arithmetic identical to what the device would compute
@@ -37,6 +40,8 @@ inline MarchParams make_march_params(const uint8_t* bitfield, int cascades, floa
   p.dt_min = sqrt3 / (float)max_samples;
   volatile float num = two_sqrt3 * dt_scale;
   p.dt_max = num / (float)grid_size;
+  uint32_t sb; memcpy(&sb, &scale, 4);
+  p.pow2_scale = (sb & 0x007fffffu) == 0u && (sb >> 23) > 1u && (sb >> 23) < 253u;
   return p;
 }
 

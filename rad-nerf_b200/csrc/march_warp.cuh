@@ -42,7 +42,8 @@ __device__ __forceinline__ CellProbe probe_cell(const Ray& r, const MarchParams&
     const int md = min(p.cascades - 1, max(0, frexp_exponent(fabsf(__fmul_rn(s.dt, p.gs_f)))));
     mip = max(mp, md);
     mip_bound = fminf(__uint_as_float((uint32_t)(mip - 1 + 127) << 23), p.scale);
-    mip_bound_inv = __fdiv_rn(1.0f, mip_bound);
+    // 1 / 2^k = 2^-k exactly: the same bits as the IEEE division, without its dozen instructions per probe
+    mip_bound_inv = p.pow2_scale ? __uint_as_float(0x7f000000u - __float_as_uint(mip_bound)) : __fdiv_rn(1.0f, mip_bound);
   }
   const int nx = (int)fmaxf(0.0f, fminf(__fmul_rn(__fmul_rn(0.5f, __fmaf_rn(s.x, mip_bound_inv, 1.0f)), p.gs_f), p.gs_m1));
   const int ny = (int)fmaxf(0.0f, fminf(__fmul_rn(__fmul_rn(0.5f, __fmaf_rn(s.y, mip_bound_inv, 1.0f)), p.gs_f), p.gs_m1));
