@@ -466,7 +466,7 @@ def run_product(args):
         traffic = None
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", TRAFFIC_JSON)))["kernels"]
-            kname = {"field_bwd": "field_bwd_tc_kernel", "field_fwd": "field_fwd_tc_kernel<1>", "march": "eng_march_kernel<1>",
+            kname = {"field_bwd": "field_bwd_tc_kernel<7>", "field_fwd": "field_fwd_tc_kernel<1>", "march": "eng_march_kernel<1>",
                      "adam": "eng_adam_kernel"}.get(top)
             if kname in tj and args.workload == "radnerf_tat_k2" and tr.engine is not None:
                 traffic = tj[kname]["dram_bytes_per_launch"]
@@ -477,6 +477,19 @@ def run_product(args):
                      "launch_ms": t_ms, "share_of_step": t_ms * stage_ms[top][1] / args.steps / ms_step,
                      "stage_ms_per_launch": {k: round(v[0], 4) for k, v in stage_ms.items()},
                      "stages_share_of_step": sum(v[0] * v[1] for v in stage_ms.values()) / args.steps / ms_step})
+        # what actually bounds the field kernels: scattered accesses to the L2-resident tables.  Reference rates from the
+        # microbenchmark (scripts/microbench_l2.py), sector counts per sample from the ncu capture of this build (profiles/)
+        try:
+            ref = json.load(open(os.path.join(ROOT, "profiles", "r02_l2_roofline_refs.json")))
+            if "field_bwd" in stage_ms and args.workload == ref.get("workload"):
+                t_b = stage_ms["field_bwd"][0] * 1e-3
+                ach = ref["bwd_red_sectors_per_sample"] * N / t_b / 1e9
+                roof["l2_scatter"] = {"kernel": "field_bwd", "what": "32-byte reduction sectors/s into the fp32 gradient table (L2)",
+                                      "achieved": ach, "peak": ref["red_peak_G_per_s"], "unit": "G sectors/s",
+                                      "frac": ach / ref["red_peak_G_per_s"], "sectors_per_sample": ref["bwd_red_sectors_per_sample"],
+                                      "source": ref["source"]}
+        except (OSError, KeyError, ValueError):
+            pass
         line["roofline"] = roof
     if replica is not None:
         line["replica_check"] = replica["status"]

@@ -46,9 +46,18 @@ def slim_ckpt(ckpt_path, save_poses=False):
 
 def save_ckpt(path, model, gate=None, extra=None, engine=None):
     """Writes {'state_dict': {'model.*': ..., 'ray_gate.*': ...}} -- the key layout of the reference's Lightning module
-    (train_ml.py: self.model, self.ray_gate).  With a sharded multi-GPU optimizer the fp32 masters are gathered first."""
+    (train_ml.py: self.model, self.ray_gate).
+
+    Multi-GPU (sharded optimizer): the fp32 masters are current only inside each rank's shard, so they are gathered first --
+    a COLLECTIVE.  Call save_ckpt on EVERY rank (all of them enter the gather); only rank 0 writes the file.  Calling it on
+    rank 0 alone would deadlock in the gather, so that is refused when it can be detected (path=None on the other ranks is
+    the explicit way to say "I only take part in the gather")."""
+    import torch.distributed as dist
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
     if engine is not None:
         engine.gather_master()
+    if multi and (path is None or dist.get_rank() != 0):
+        return
     sd = {f"model.{k}": v.detach().cpu() for k, v in model.state_dict().items()}
     if gate is not None:
         sd.update({f"ray_gate.{k}": v.detach().cpu() for k, v in gate.state_dict().items()})

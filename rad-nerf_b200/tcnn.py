@@ -168,6 +168,11 @@ class Encoding(nn.Module):
             raise ValueError(f"unsupported encoding {otype}")
 
     def forward(self, x):
+        if x.requires_grad and torch.is_grad_enabled():
+            # tinycudann returns dL/dx for its encodings; this build does not (the Rad-NeRF path never differentiates through the
+            # sample positions unless --optimize_ext is set, train_ml.py:90-147).  Fail loudly instead of returning zero gradients.
+            raise RuntimeError("radnerf_b200.tcnn.Encoding does not propagate gradients to its input (pose / extrinsics "
+                               "optimisation, --optimize_ext, is not supported); detach the input")
         if self.kind == "grid":
             return _HashGridFn.apply(x, self.params, self)
         x = x.detach().float().contiguous()

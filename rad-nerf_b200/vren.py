@@ -76,11 +76,13 @@ _scratch_cache = {}
 
 
 def _scratch(dev, numel):
-    """Per-device reusable fp32 scratch (the marcher's per-ray sample-t rows)."""
-    buf = _scratch_cache.get(dev)
+    """Reusable fp32 scratch (the marcher's per-ray sample-t rows), one per (device, stream): callers on different streams
+    of one device (a side-stream evaluation during training) must not share it."""
+    key = (dev, torch.cuda.current_stream(dev).cuda_stream)
+    buf = _scratch_cache.get(key)
     if buf is None or buf.numel() < numel:
         buf = torch.empty(max(numel, 1), dtype=torch.float32, device=dev)
-        _scratch_cache[dev] = buf
+        _scratch_cache[key] = buf
     return buf
 
 
