@@ -26,7 +26,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-BATCH = 8192
+BATCH = int(os.environ.get("RNB_BENCH_BATCH", "8192"))      # rays per step (BASELINE: 8192; the override is for debugging small shards)
 N_BATCHES = 8          # distinct pre-generated batches cycled through
 TRAFFIC_JSON = "r02_traffic.json"   # ncu --set full DRAM bytes per launch of the current build (scripts/profile_round.sh)
 
@@ -304,6 +304,11 @@ def run_product(args):
         return float(ms)
 
     ahead = tr.engine is not None and not args.no_march_ahead
+    trace = os.environ.get("RNB_BENCH_TRACE") == "1"
+
+    def mark(what):      # progress markers on stderr (RNB_BENCH_TRACE=1): where a multi-rank run stops, if it does
+        if trace:
+            print(f"[bench rank {rank}] {what}", file=sys.stderr, flush=True)
 
     def flush_l2():
         # evict L2 between steps (inputs are smaller than L2).  When the next batch is marched ahead on the side stream,
@@ -382,25 +387,29 @@ def run_product(args):
         # step's own kernels leave free instead of delaying them
         torch.cuda.synchronize()
         torch.cuda.set_stream(torch.cuda.Stream(priority=-1))
+    mark("set-up done")
     for s in range(args.warmup):
         dev_step(s)
+    torch.cuda.synchronize(); mark("warm-up done")
     # time the L2 flush alone so that it can be subtracted (it is not part of the step)
     flush_ms = timed(lambda s: flush.add_(1.0), args.steps) / args.steps
     clocks = ClockSampler(local); clocks.start()
     n0 = _lib.launch_count
-    ms = timed(dev_step, args.steps)
+    ms = timed(lambda s: dev_step(s + args.warmup), args.steps)      # (indices continue: the batch marched ahead is the next one trained)
     launches = _lib.launch_count - n0
     clk = clocks.stop()
     ms_step = ms / args.steps - flush_ms
+    mark("timed steps done")
     # the same loop without the L2 flush (nothing subtracted): parameters and inputs of the previous step stay in L2
     def noflush_step(s):
         nxt = dev[(s + 1) % len(dev)]
         tr.step(*dev[s % len(dev)], next_rays=(nxt if use_graph else nxt[:2]) if ahead else None)
-    noflush_step(0)
-    ms_noflush = timed(lambda s: noflush_step(s + 1), args.steps) / args.steps
+    noflush_step(args.warmup + args.steps)
+    ms_noflush = timed(lambda s: noflush_step(s + 1 + args.warmup + args.steps), args.steps) / args.steps
     for s in range(args.warmup):         # untimed: feeder slots, copy / read-back streams and pinned buffers come up here
         e2e_step(s)
     e2e_ms = timed(lambda s: e2e_step(s + args.warmup), args.steps) / args.steps - flush_ms
+    mark("noflush + e2e done")
     # per-stage device time of the same steps (separate pass: CUDA events around every stage of the fused step)
     stage_ms = {}
     if tr.engine is not None:
@@ -413,6 +422,7 @@ def run_product(args):
         lib.rnb_engine_profile_read(arr_ms, arr_n, 16)
         lib.rnb_engine_profile(0)
         stage_ms = {STAGES[i]: (arr_ms[i] / max(arr_n[i], 1), arr_n[i]) for i in range(len(STAGES)) if arr_n[i]}
+    mark("stage profile done")
     # multi-rank correctness the driver can see: every rank must hold bit-identical fp16 parameters after the timed steps
     # (one writer per shard in the peer-memory optimizer) and must have seen the same global gate importance
     replica = None
@@ -579,6 +589,128 @@ def run_product_fwd_only(args):
     print(json.dumps(line))
 
 
+def run_render(args):
+    """Test-time frames (ml_render(test_time=True), ml_rendering.py:81-155): one step = one full frame of the workload's shape,
+    image rows interleaved over the ranks (parallel.frame_rows), random-init parameters (no early termination: worst case).
+    metric render_rays_per_s = H * W / frame time (ms_per_step is the frame time: BASELINE.json's "800^2 render ms")."""
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    syn, w = workload(args.workload)
+    K, H, W = w["K"], w["H"], w["W"]
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        # the oracle's frame loop (oracle/render_cpu.render_test per sub-NeRF + gate blend) on a bounded sample of the frame's rays
+        from oracle import render_cpu as R
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        n = max(512, 4096 // K)          # a frame's worth of K alive-ray loops on the CPU takes minutes: bounded sample
+        cam = syn.make_cameras(100, w["radius"], H, W, w["fx"])
+        o, d = syn.full_image_rays(cam, 3)
+        sel = np.random.RandomState(0).choice(len(o), n, replace=False)
+        o, d = np.ascontiguousarray(o[sel]), np.ascontiguousarray(d[sel])
+        P = R.FieldParams(w["scale"], K, seed=0)
+        bfs = scene_bitfields(syn, w)
+
+        def frame():
+            with torch.no_grad():
+                g = R.gate(P, torch.from_numpy(o), torch.from_numpy(d))[0].numpy() if K > 1 else np.ones((n, 1), np.float32)
+                rgb = np.zeros((n, 3), np.float32)
+                for i in range(K):
+                    rgb += g[:, i:i + 1] * R.render_test(P, o, d, bfs[i], i, 1, 0.0)["rgb"]
+            return rgb
+        for _ in range(args.warmup):
+            frame()
+        ts = []
+        for _ in range(max(args.steps, 1)):
+            t0 = time.perf_counter(); frame(); ts.append(time.perf_counter() - t0)
+        med = float(np.median(ts))
+        cb = {"value": n / med, "unit": "rays/s", "cores": cores, "kind": "port",
+              "sample": f"{n} of {H * W} rays of the frame per step (fixed), K = {K} alive-ray loops + gate blend; median of {len(ts)}"}
+        print(json.dumps({"impl": "reference", "metric": "render_rays_per_s", "value": n / med, "unit": "rays/s", "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * med, "higher_is_better": True, "scaling": "strong",
+                          "vs_baseline": None, "dtype": "f32 (fp16 rounding points)", "data": "synthetic", "config": arm_config(args, w, args.gpus),
+                          "cpu_baseline": cb, "e2e": {"value": n / med, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from radnerf_b200 import _lib, parallel
+    from radnerf_b200.trainer import Trainer
+    _lib.lib()
+    tr = Trainer(scale=w["scale"], K=K, freeze_occupancy=True, device=f"cuda:{local}", engine=True, batch_rays=8192)
+    tr.set_occupancy(scene_bitfields(syn, w))
+    cam = syn.make_cameras(100, w["radius"], H, W, w["fx"])
+    o, d = syn.full_image_rays(cam, 3)
+    rows = parallel.frame_rows(H)
+    sel = (rows[:, None] * W + torch.arange(W)[None, :]).reshape(-1)
+    ho = torch.from_numpy(o)[sel].contiguous().pin_memory(); hd = torch.from_numpy(d)[sel].contiguous().pin_memory()
+    do, dd = ho.cuda(), hd.cuda()
+    out_pin = torch.zeros(len(sel), 3).pin_memory()
+    spr = int(os.environ.get("RNB_RENDER_SPR", "32"))
+    last = {}
+
+    def frame(src_o, src_d, to_host):
+        if to_host:
+            src_o, src_d = src_o.cuda(non_blocking=True), src_d.cuda(non_blocking=True)
+        res = tr.engine.render(src_o, src_d, samples_per_ray=spr)
+        last.update(samples=res["total_samples"], rounds=res["rounds"])
+        if world > 1:
+            full = parallel.gather_frame(torch.cat([res["rgb"], res["opacity"][:, None], res["depth"]], 1), H, W)
+            assert full.shape[0] == H * W
+        if to_host:
+            out_pin.copy_(res["rgb"], non_blocking=True)
+
+    def timed(fn, steps):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(); torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / steps], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+    for _ in range(args.warmup):
+        frame(do, dd, False)
+    clocks = ClockSampler(local); clocks.start()
+    n0 = _lib.launch_count
+    ms = timed(lambda: frame(do, dd, False), args.steps)
+    launches = _lib.launch_count - n0
+    clk = clocks.stop()
+    e2e_ms = timed(lambda: frame(ho, hd, True), args.steps)
+    smp = torch.tensor([float(last["samples"])], device="cuda")
+    if world > 1:
+        dist.all_reduce(smp)
+    if rank == 0:
+        hbm, tflops, which = measured_peaks()
+        ns = float(smp)
+        line = {"metric": "render_rays_per_s", "value": H * W / (ms * 1e-3), "unit": "rays/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f16 (fp32 accumulate; fp32 march/composite)", "data": "synthetic", "config": arm_config(args, w, world),
+                "run": {"frame": f"{W}x{H}", "frame_ms": ms, "samples": int(ns), "rounds": int(last["rounds"]), "samples_per_round": spr,
+                        "sharding": "interleaved rows; all_gather of (3+1+K) floats per ray" if world > 1 else "single GPU",
+                        "l2": "working set (rays, samples of a round) larger than L2: no flush"},
+                "clocks": clk, "gpu_launches": launches,
+                "e2e": {"value": H * W / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": int(2 * len(sel) * 12),
+                        "d2h_bytes_per_step": int(len(sel) * 12), "ms_per_step": e2e_ms},
+                "roofline": {"kernel": "frame (inf_march + field_fwd_tc_kernel<0> + inf_composite, all rounds)", "bound": "tensor",
+                             "achieved": 18944 * ns / (ms * 1e-3) / 1e12, "peak": tflops, "unit": "TFLOP/s",
+                             "frac": 18944 * ns / (ms * 1e-3) / 1e12 / tflops, "traffic": None, "peak_source": which,
+                             "hbm_frac": (34 + 24 + 32) * ns / (ms * 1e-3) / 1e9 / hbm,
+                             "note": "bounded by scattered L2 gathers (128 per sample): %.0f G gathers/s against 282 G/s from L2 "
+                                     "(profiles/r02_microbench_l2.jsonl); coarse levels hit L1" % (128 * ns / (ms * 1e-3) / 1e9)}}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def _json_lines(cmd, timeout):
     import subprocess as sp
     out = sp.run(cmd, capture_output=True, text=True, timeout=timeout)
@@ -632,7 +764,9 @@ def main():
     ap.add_argument("--python-surface", action="store_true", help="time the drop-in Python operator surface instead of the fused engine")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
-    if args.impl == "reference":
+    if workload(args.workload)[1].get("infer"):
+        run_render(args)
+    elif args.impl == "reference":
         run_reference(args)
     elif workload(args.workload)[1].get("forward_only"):
         run_product_fwd_only(args)

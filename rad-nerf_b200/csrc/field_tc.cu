@@ -103,7 +103,8 @@ struct TcSmem {
   static constexpr int wg0 = (wend + 127) / 128 * 128;
   static constexpr int bars = wg0 + kWG * per_wg;       // kWG mbarriers
   static constexpr int tmem_slot = bars + kWG * 8;
-  static constexpr int bytes = tmem_slot + 16;
+  static constexpr int extent = tmem_slot + 16;          // i64 [2]: this pass's base and end, read ONCE per CTA
+  static constexpr int bytes = extent + 16;
 };
 
 // D[tmem] = A[128 x KDIM] * W[N x KDIM]^T, issued by one thread
@@ -181,14 +182,19 @@ __global__ void __maxnreg__(96) field_fwd_tc_kernel(TcFieldArgs A, __half* __res
   const int K = A.K;
   int64_t tiles_before = 0;
   if (kSave && l2_stream) l2_stream = tc::l2_evict_first_policy();
+  volatile int64_t* extent = reinterpret_cast<volatile int64_t*>(smem + TcSmem::extent);
   for (int pass = 0; pass < K; pass++) {
-    const int64_t base = __ldg(A.seg + pass);
-    int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
+    // The pass extents are read by ONE thread and shared: every barrier below is taken (or skipped) by the whole CTA even if the
+    // sample list is being rewritten under the kernel (a caller error, but it must not hang the GPU).
+    __syncthreads();
+    if (tid == 0) { extent[0] = __ldg(A.seg + pass); extent[1] = extent[0] + __ldg(A.seg + K + 1 + pass); }
+    __syncthreads();
+    const int64_t base = extent[0];
+    int64_t pass_end = extent[1];
     if (pass_end > A.capacity) pass_end = A.capacity;
     const int64_t n_tiles = pass_end > base ? (pass_end - base + kRows - 1) / kRows : 0;
     if (n_tiles == 0) continue;      // (CTA-uniform) an empty pass -- e.g. every round behind the end of a frame -- costs nothing
     // ---- stage this pass's weights (whole CTA) ----
-    __syncthreads();
     {
       const __half* gw = A.geo_w[pass];
       const __half* rw = A.rgb_w[pass];
@@ -490,7 +496,8 @@ struct TcBwdSmem {
   static constexpr int bars = wg0 + kWGB * per_wg;                // full[kWGB], done[kWGB], loaded[kWGB][2]
   static constexpr int tmem_slot = bars + 4 * kWGB * 8;
   static constexpr int ready = tmem_slot + 16;                    // i32 [kWGB][4]: tiles of this pass whose d(encoding) rows were handed over
-  static constexpr int bytes = ready + kWGB * 4 * 4;
+  static constexpr int extent = ready + kWGB * 4 * 4;            // i64 [2]: this pass's base and end, read ONCE per CTA
+  static constexpr int bytes = extent + 16;
 };
 // Scatter warps.  The table scatter (16 levels x 8 corners of reductions per sample, plus the run aggregation on the
 // coarse levels) used to run in the compute warpgroups behind the five MMA round trips of a tile: a warp was either in its
@@ -639,13 +646,18 @@ __global__ void __launch_bounds__(bwd_threads(kScatterWarps), 1) field_bwd_tc_ke
 #define ph_done ra
 #define q_load rb
   int64_t tiles_before = 0;
+  volatile int64_t* extent = reinterpret_cast<volatile int64_t*>(smem + TcBwdSmem::extent);
   for (int pass = 0; pass < K; pass++) {
-    const int64_t base = __ldg(A.seg + pass);
-    int64_t pass_end = base + __ldg(A.seg + K + 1 + pass);
+    // ONE read of the pass extents per CTA: the compute warpgroups, the scatter warps and the issuer all derive their tile
+    // counts from them and wait for each other on that basis -- they must agree even if the list is rewritten under the kernel
+    __syncthreads();
+    if (tid == 0) { extent[0] = __ldg(A.seg + pass); extent[1] = extent[0] + __ldg(A.seg + K + 1 + pass); }
+    __syncthreads();
+    const int64_t base = extent[0];
+    int64_t pass_end = extent[1];
     if (pass_end > A.capacity) pass_end = A.capacity;
     const int64_t n_tiles = pass_end > base ? (pass_end - base + kRows - 1) / kRows : 0;
     // ---- stage this pass's weights (whole CTA) ----
-    __syncthreads();
     {
       const __half* gw = A.geo_w[pass];
       const __half* rw = A.rgb_w[pass];

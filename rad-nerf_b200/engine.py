@@ -247,6 +247,12 @@ class Engine:
             self._march_stream = torch.cuda.Stream(self.device)
         # the batch being (or about to be) trained sits in the slot of its own prefetch if that is still pending, else in
         # self._slot (forward_backward has already claimed it)
+        if slot is None and getattr(self, "_in_step", False):
+            # called from forward_backward: the batch being trained sits in self._slot whatever the bookkeeping of older
+            # prefetches says; an entry still parked in the other slot was never picked up (stale): let it finish, forget it
+            slot = self._slot ^ 1
+            for k in [k for k, v in self._ahead.items() if v[0] == slot]:
+                torch.cuda.current_stream(self.device).wait_event(self._ahead.pop(k)[4])
         busy = next(iter(self._ahead.values()))[0] if self._ahead else self._slot
         slot = (busy ^ 1) if slot is None else slot
         cur = torch.cuda.current_stream(self.device)
@@ -284,8 +290,9 @@ class Engine:
             # not marched ahead: march here, into the slot no prefetch is using.  Entries older than the newest one
             # were never picked up (the caller changed its mind): let them finish, then forget them.
             keys = list(self._ahead)
-            for k in keys[:-1]:
+            for k in (keys if next_rays is not None else keys[:-1]):      # (next_rays given: this step prefetches itself, all are stale)
                 cur.wait_event(self._ahead.pop(k)[4])
+            keys = list(self._ahead)
             march_slot = (self._ahead[keys[-1]][0] ^ 1) if keys else 0
             if getattr(self, "_force_slot", None) is not None:      # (graph replay: static batch slot == march slot)
                 march_slot = self._force_slot
@@ -318,7 +325,11 @@ class Engine:
                 call("rnb_engine_gate", ctypes.byref(c), self.ws, self.flat16, rays_o, rays_d, st)
                 parallel.allreduce_sum_(self.importance)     # CV loss is non-linear in the batch: the importance must be global (8e)
         if next_rays is not None:
-            self.prefetch(next_rays[0], next_rays[1])
+            self._in_step = True
+            try:
+                self.prefetch(next_rays[0], next_rays[1])
+            finally:
+                self._in_step = False
         bfs = self.bitfields()
         bf_arr = (ctypes.c_void_p * self.K)(*[b.data_ptr() for b in bfs])
         bg_arr = (ctypes.c_float * (3 * self.K))(*[float(x) for row in bg for x in row])

@@ -203,7 +203,9 @@ WORKLOADS = {
     "ngp_blender_k1": dict(scale=0.5, K=1, H=800, W=800, fx=1111.1, radius=1.5),
     "radnerf_tat_k2": dict(scale=0.5, K=2, H=1080, W=1920, fx=1166.0, radius=0.9),   # radius tuned: ~33 samples/ray
     "radnerf_360_k4": dict(scale=16.0, K=4, H=822, W=1237, fx=1050.0, radius=1.0),
-    "radnerf_tat_k8_infer": dict(scale=0.5, K=8, H=1080, W=1920, fx=1166.0, radius=0.9),
+    # test-time frames (BASELINE.json's second metric / configs[4]): one step = one full frame, rows sharded over the ranks
+    "radnerf_tat_k8_infer": dict(scale=0.5, K=8, H=1080, W=1920, fx=1166.0, radius=0.9, infer=True),
+    "ngp_blender_k1_infer": dict(scale=0.5, K=1, H=800, W=800, fx=1111.1, radius=1.5, infer=True),
 }
 
 

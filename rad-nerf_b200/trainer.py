@@ -4,11 +4,13 @@ process per GPU, the step of train_ml.py:172-200 --
     every 16 steps: update_density_grid            (train_ml.py:173-177)
     ml_render(model, gate, rays_o, rays_d)         (ml_rendering.py:11-78)
     NeRFLoss: rgb + opacity + cv_importance + depth_mutual, loss = sum of term means
-    backward -> [all-reduce of the flat gradient bucket over NCCL when world_size > 1] -> Adam(eps=1e-15)
+    backward -> gradient exchange when world_size > 1 -> Adam(eps=1e-15)
 
-Rays shard naturally: with world_size W each rank renders its own slice of the global batch;
-the only exchange is one all-reduce (sum) of the gradients, plus the K-float gating importance
-before the (non-linear) CV loss.
+Rays shard naturally: with world_size W each rank renders its own slice of the global batch.  Exchanges per step: the
+K-float gating importance before the (non-linear) CV loss (an NCCL all-reduce), and the gradients -- with the fused engine
+ONE kernel over NVLink peer memory (csrc/peer.cu: reduce-scatter + Adam + fp16 all-gather, flag barriers in peer memory);
+the Python operator surface (engine=False) all-reduces one flat gradient bucket over NCCL instead.
+graph=True replays the single-process step from captured CUDA graphs (engine.GraphStepper).
 """
 from __future__ import annotations
 

@@ -13,7 +13,7 @@ from bench import scene_bitfields, workload  # noqa: E402
 
 
 def main():
-    fitted = "--fitted" in sys.argv
+    fitted = any(a.startswith("--fitted") for a in sys.argv)
     names = [a for a in sys.argv[1:] if not a.startswith("--")]
     name = names[0] if names else "radnerf_tat_k8_infer"
     spr = int(os.environ.get("RNB_RENDER_SPR", "32"))
@@ -27,20 +27,17 @@ def main():
     tr = Trainer(scale=w["scale"], K=w["K"], freeze_occupancy=True, device=f"cuda:{local}", engine=True, batch_rays=8192)
     tr.set_occupancy(scene_bitfields(syn, w))
     if fitted:
-        # rank 0 trains 2000 steps on the analytic scene; parameters and occupancy are broadcast (SURVEY 8d "fitted" state)
+        # SURVEY 8d "fitted" state: 2000 training steps on the analytic scene.  The fit is a SINGLE-PROCESS job (its engine must
+        # not be a data-parallel one: a rank-0-only fit with a sharded engine waits for collectives nobody joins), so it has
+        # to be produced beforehand: python scripts/fit_scene.py --K 8 --save fitted_k8.pt, then pass --fitted=fitted_k8.pt
+        path = [a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--fitted=")]
+        assert path, "--fitted=<file written by scripts/fit_scene.py --save>"
+        st = torch.load(path[0], map_location=f"cuda:{local}")
         eng = tr.engine
-        if rank == 0:
-            sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
-            from fit_scene import fit
-            _, src = fit(steps=2000, K=w["K"], return_trainer=True)
-            with torch.no_grad():
-                eng.flat.copy_(src.engine.flat)
-                for a, b in zip(eng.grids() + eng.bitfields(), src.engine.grids() + src.engine.bitfields()):
-                    a.copy_(b)
-            del src
-        if world > 1:
-            for t in [eng.flat] + eng.grids() + eng.bitfields():
-                dist.broadcast(t, 0)
+        with torch.no_grad():
+            eng.flat.copy_(st["flat"])
+            for a, b in zip(eng.grids() + eng.bitfields(), st["grids"] + st["bitfields"]):
+                a.copy_(b)
         for _, m in eng._mods:
             m._shadow.version = None
         eng.sync_params()

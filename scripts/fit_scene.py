@@ -73,5 +73,9 @@ if __name__ == "__main__":
     ap.add_argument("--res", type=int, default=200)
     ap.add_argument("--batch", type=int, default=8192)
     ap.add_argument("--log-every", type=int, default=250)
+    ap.add_argument("--save", default=None, help="write the fitted flat parameters, grids and bitfields (bench_render_dist.py --fitted=FILE)")
     a = ap.parse_args()
-    print(json.dumps(fit(a.steps, a.K, a.res, a.batch, log_every=a.log_every)))
+    info, tr = fit(a.steps, a.K, a.res, a.batch, log_every=a.log_every, return_trainer=True)
+    if a.save:
+        torch.save({"flat": tr.engine.flat, "grids": tr.engine.grids(), "bitfields": tr.engine.bitfields(), "info": info}, a.save)
+    print(json.dumps(info))
