@@ -647,7 +647,6 @@ class GraphStepper:
         self.slots = [tuple(torch.zeros(n, 3, device=dev) for _ in range(3)) for _ in range(2)]
         self.graphs, self.launches = {}, {}
         self._key = None
-        self._lr_pin = torch.zeros(1, dtype=torch.float32).pin_memory()
         self._pool = None
         self._warm = False
         self.replays = 0
@@ -681,8 +680,12 @@ class GraphStepper:
         e = self.e
         v = float(e.lr if lr is None else lr)
         if force or v != getattr(self, "_lr_dev", None):       # (a constant rate is written once)
-            self._lr_pin = torch.tensor([v], dtype=torch.float32).pin_memory()      # fresh pinned word: the previous copy may be in flight
-            e.status[8:9].view(torch.float32).copy_(self._lr_pin, non_blocking=True)
+            if getattr(self, "_lr_ring", None) is None:
+                self._lr_ring, self._lr_k = torch.zeros(64, dtype=torch.float32).pin_memory(), 0
+            k = self._lr_k % 64                                  # a ring of pinned words: an earlier copy may still be in flight
+            self._lr_k += 1
+            self._lr_ring[k] = v
+            e.status[8:9].view(torch.float32).copy_(self._lr_ring[k:k + 1], non_blocking=True)
             self._lr_dev = v
 
     def _capture(self, slot, kind):
