@@ -178,7 +178,7 @@ class Engine:
         self._ahead = {}                # (rays_o ptr, rays_d ptr) -> (slot, rays_o, rays_d, noise, done_event)
         self._slot = 0                  # slot holding the samples of the batch last trained on
 
-    def _alloc_workspace(self):
+    def _alloc_workspace(self, carry_status=None):
         """Carve the workspace for cfg.sample_capacity and (re)create the tensor views of its regions."""
         c, K = self.cfg, self.K
         L = _Layout()
@@ -199,8 +199,8 @@ class Engine:
         self.loss = v("loss", torch.float32, (8,))
         self.status = v("status", torch.int32, (16,))
         self.status.zero_()
-        if any(self._status_seen):        # re-allocation (capacity growth): carry the counters over
-            self.status[:4] = torch.tensor(self._status_seen, dtype=torch.int32, device=self.device)
+        if carry_status is not None:      # re-allocation (capacity growth): counters, noise-stream positions and lr carry over
+            self.status.copy_(carry_status)
 
     def _view(self, name, dtype, shape):
         off = getattr(self.layout, name)
@@ -459,9 +459,12 @@ class Engine:
         """Re-allocate the workspace for at least `min_capacity` samples (on_overflow='grow')."""
         torch.cuda.synchronize(self.device)
         self._ahead.clear()
+        old = self.status.clone()          # (the device is idle: this is the exact state, not the host's lagging copy)
+        self._status_seen = old[:4].tolist()
         self.cfg.sample_capacity = (max(int(min_capacity), self.cfg.sample_capacity) + 127) // 128 * 128
         self.samples_per_ray = self.cfg.sample_capacity // (self.n_rays * self.K)
-        self._alloc_workspace()
+        self._alloc_workspace(carry_status=old)
+        self._status_ring = None           # pending read-backs refer to the old block
         self._render_cache = None
 
     def guard_status(self):
